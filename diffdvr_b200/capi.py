@@ -1,0 +1,335 @@
+"""ctypes mirror of ``include/dvr_b200.h`` (the C-ABI of the B200 ray marcher).
+
+Host-side plumbing only: builds the plain-C structs from torch tensors (device memory,
+strides) and calls ``libdvr_b200.so``.  There is NO CPU fallback: if the CUDA library is not
+built, loading raises.  The struct classes are also what the tests use to drive the CPU
+oracles (which export the same signatures with host pointers) -- the oracle itself is never
+imported from here.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Optional, Sequence
+
+DVR_MAX_DIMS = 5
+DVR_OK = 0
+DVR_ERR_INVALID_ARGUMENT = -1
+DVR_ERR_UNSUPPORTED = -2
+DVR_ERR_CUDA = -3
+
+# enum values of renderer/renderer_settings.cuh:81-146
+FILTER_NEAREST, FILTER_TRILINEAR, FILTER_PRESHADED, FILTER_NETWORK = 0, 1, 3, 4
+CAMERA_RAY_START_DIR, CAMERA_INVERSE_VIEW_MATRIX, CAMERA_REFERENCE_FRAME = 0, 1, 2
+TF_IDENTITY, TF_TEXTURE, TF_LINEAR, TF_GAUSSIAN, TF_PRESHADED, TF_GAUSSIAN_LOG = 0, 1, 2, 3, 5, 6
+BLEND_BEER_LAMBERT, BLEND_ALPHA = 0, 1
+
+
+class DvrTensor(ctypes.Structure):
+    _fields_ = [
+        ("ptr", ctypes.c_void_p),
+        ("ndim", ctypes.c_int32),
+        ("size", ctypes.c_int64 * DVR_MAX_DIMS),
+        ("stride", ctypes.c_int64 * DVR_MAX_DIMS),
+    ]
+
+
+class DvrInputs(ctypes.Structure):
+    _fields_ = [
+        ("screen_width", ctypes.c_int32),
+        ("screen_height", ctypes.c_int32),
+        ("volume_filter_mode", ctypes.c_int32),
+        ("volume", DvrTensor),
+        ("box_min", DvrTensor),
+        ("box_min_value", ctypes.c_float * 3),
+        ("box_size", DvrTensor),
+        ("box_size_value", ctypes.c_float * 3),
+        ("camera_mode", ctypes.c_int32),
+        ("camera_ray_start", DvrTensor),
+        ("camera_ray_dir", DvrTensor),
+        ("camera_matrix", DvrTensor),
+        ("camera_matrix_value", ctypes.c_float * 16),
+        ("camera_fov_y_radians", ctypes.c_float),
+        ("step_size", DvrTensor),
+        ("step_size_value", ctypes.c_float),
+        ("tf_mode", ctypes.c_int32),
+        ("tf", DvrTensor),
+        ("blend_mode", ctypes.c_int32),
+        ("blending_early_out", ctypes.c_float),
+    ]
+
+
+class DvrOutputs(ctypes.Structure):
+    _fields_ = [("color", DvrTensor), ("termination_index", DvrTensor)]
+
+
+class DvrForwardDifferencesSettings(ctypes.Structure):
+    _fields_ = [
+        ("D", ctypes.c_int32),
+        ("d_stepsize", ctypes.c_int32),
+        ("d_ray_start", ctypes.c_int32 * 3),
+        ("d_ray_dir", ctypes.c_int32 * 3),
+        ("d_tf", DvrTensor),
+        ("has_tf_derivatives", ctypes.c_int32),
+    ]
+
+
+class DvrAdjointOutputs(ctypes.Structure):
+    _fields_ = [
+        ("has_volume_derivatives", ctypes.c_int32),
+        ("adj_volume", DvrTensor),
+        ("has_stepsize_derivatives", ctypes.c_int32),
+        ("adj_step_size", DvrTensor),
+        ("has_camera_derivatives", ctypes.c_int32),
+        ("adj_camera_ray_start", DvrTensor),
+        ("adj_camera_ray_dir", DvrTensor),
+        ("has_tf_derivatives", ctypes.c_int32),
+        ("tf_delayed_accumulation", ctypes.c_int32),
+        ("adj_tf", DvrTensor),
+    ]
+
+
+def tensor_view(t) -> DvrTensor:
+    """DvrTensor over a torch tensor or numpy array (no copy; keep ``t`` alive)."""
+    v = DvrTensor()
+    if t is None:
+        return v
+    if hasattr(t, "data_ptr"):  # torch
+        v.ptr = t.data_ptr()
+        shape, strides = tuple(t.shape), tuple(t.stride())
+    else:  # numpy
+        v.ptr = t.ctypes.data
+        shape = tuple(t.shape)
+        strides = tuple(s // t.itemsize for s in t.strides)
+    if len(shape) > DVR_MAX_DIMS:
+        raise ValueError("too many dimensions")
+    v.ndim = len(shape)
+    for i, (n, s) in enumerate(zip(shape, strides)):
+        v.size[i] = n
+        v.stride[i] = s
+    return v
+
+
+def _is_tensor(x) -> bool:
+    return hasattr(x, "shape") and not isinstance(x, (tuple, list))
+
+
+class Inputs:
+    """Python-side description of ``RendererInputsHost`` (renderer/renderer.h:20-64).
+
+    Scalar-or-tensor fields (box_min, box_size, step_size, camera matrix) accept either kind,
+    like the std::variant members of the reference struct.
+    """
+
+    def __init__(self, *, screen_size, volume, box_min, box_size, camera_mode, step_size, tf_mode,
+                 tf, blend_mode=BLEND_BEER_LAMBERT, volume_filter_mode=FILTER_TRILINEAR,
+                 camera_ray_start=None, camera_ray_dir=None, camera_matrix=None,
+                 camera_fov_y_radians=0.0, blending_early_out=1.0 - 1e-5):
+        self.screen_size = tuple(screen_size)  # (W, H)
+        self.volume = volume
+        self.box_min = box_min
+        self.box_size = box_size
+        self.camera_mode = camera_mode
+        self.camera_ray_start = camera_ray_start
+        self.camera_ray_dir = camera_ray_dir
+        self.camera_matrix = camera_matrix
+        self.camera_fov_y_radians = camera_fov_y_radians
+        self.step_size = step_size
+        self.tf_mode = tf_mode
+        self.tf = tf
+        self.blend_mode = blend_mode
+        self.volume_filter_mode = volume_filter_mode
+        self.blending_early_out = blending_early_out
+
+    def to_c(self) -> DvrInputs:
+        c = DvrInputs()
+        c.screen_width, c.screen_height = self.screen_size
+        c.volume_filter_mode = int(self.volume_filter_mode)
+        c.volume = tensor_view(self.volume)
+        if _is_tensor(self.box_min):
+            c.box_min = tensor_view(self.box_min)
+        else:
+            c.box_min_value[:] = [float(v) for v in self.box_min]
+        if _is_tensor(self.box_size):
+            c.box_size = tensor_view(self.box_size)
+        else:
+            c.box_size_value[:] = [float(v) for v in self.box_size]
+        c.camera_mode = int(self.camera_mode)
+        if self.camera_mode == CAMERA_RAY_START_DIR:
+            c.camera_ray_start = tensor_view(self.camera_ray_start)
+            c.camera_ray_dir = tensor_view(self.camera_ray_dir)
+        elif _is_tensor(self.camera_matrix) and len(self.camera_matrix.shape) == 3:
+            c.camera_matrix = tensor_view(self.camera_matrix)
+        else:  # 4x4 scalar variant (glm::mat4 in the reference), row-major nested sequence
+            flat = [float(v) for row in self.camera_matrix for v in row]
+            c.camera_matrix_value[:] = flat
+        c.camera_fov_y_radians = float(self.camera_fov_y_radians)
+        if _is_tensor(self.step_size):
+            c.step_size = tensor_view(self.step_size)
+        else:
+            c.step_size_value = float(self.step_size)
+        c.tf_mode = int(self.tf_mode)
+        c.tf = tensor_view(self.tf)
+        c.blend_mode = int(self.blend_mode)
+        c.blending_early_out = float(self.blending_early_out)
+        return c
+
+
+def make_outputs(color, termination_index) -> DvrOutputs:
+    o = DvrOutputs()
+    o.color = tensor_view(color)
+    o.termination_index = tensor_view(termination_index)
+    return o
+
+
+def make_fd_settings(D, d_stepsize=-1, d_ray_start=(-1, -1, -1), d_ray_dir=(-1, -1, -1), d_tf=None,
+                     has_tf_derivatives=False) -> DvrForwardDifferencesSettings:
+    s = DvrForwardDifferencesSettings()
+    s.D = int(D)
+    s.d_stepsize = int(d_stepsize)
+    s.d_ray_start[:] = [int(v) for v in d_ray_start]
+    s.d_ray_dir[:] = [int(v) for v in d_ray_dir]
+    s.d_tf = tensor_view(d_tf)
+    s.has_tf_derivatives = int(bool(has_tf_derivatives))
+    return s
+
+
+def make_adjoint_outputs(adj_volume=None, adj_step_size=None, adj_camera_ray_start=None,
+                         adj_camera_ray_dir=None, adj_tf=None,
+                         tf_delayed_accumulation=False) -> DvrAdjointOutputs:
+    a = DvrAdjointOutputs()
+    a.has_volume_derivatives = int(adj_volume is not None)
+    a.adj_volume = tensor_view(adj_volume)
+    a.has_stepsize_derivatives = int(adj_step_size is not None)
+    a.adj_step_size = tensor_view(adj_step_size)
+    a.has_camera_derivatives = int(adj_camera_ray_start is not None)
+    a.adj_camera_ray_start = tensor_view(adj_camera_ray_start)
+    a.adj_camera_ray_dir = tensor_view(adj_camera_ray_dir)
+    a.has_tf_derivatives = int(adj_tf is not None)
+    a.tf_delayed_accumulation = int(bool(tf_delayed_accumulation))
+    a.adj_tf = tensor_view(adj_tf)
+    return a
+
+
+class DvrError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"dvr error {code}: {message}")
+        self.code = code
+
+
+class Library:
+    """A loaded library exporting the dvr C-ABI under ``prefix`` (``dvr_`` for the product)."""
+
+    def __init__(self, path: str, prefix: str = "dvr_"):
+        self.path = path
+        self.prefix = prefix
+        self.lib = ctypes.CDLL(path)
+        P = ctypes.POINTER
+        self._sig("render_forward", [P(DvrInputs), P(DvrOutputs), ctypes.c_void_p])
+        self._sig("render_forward_gradients",
+                  [P(DvrInputs), P(DvrForwardDifferencesSettings), P(DvrOutputs), P(DvrTensor),
+                   ctypes.c_void_p])
+        self._sig("forward_variables_to_gradients",
+                  [P(DvrTensor), P(DvrTensor), P(DvrForwardDifferencesSettings),
+                   P(DvrAdjointOutputs), ctypes.c_void_p])
+        self._sig("render_adjoint",
+                  [P(DvrInputs), P(DvrOutputs), P(DvrTensor), P(DvrAdjointOutputs), ctypes.c_void_p])
+        f = getattr(self.lib, prefix + "last_error")
+        f.restype = ctypes.c_char_p
+        f.argtypes = []
+
+    def _sig(self, name, argtypes):
+        f = getattr(self.lib, self.prefix + name)
+        f.restype = ctypes.c_int
+        f.argtypes = argtypes
+
+    def last_error(self) -> str:
+        return getattr(self.lib, self.prefix + "last_error")().decode()
+
+    def _check(self, rc):
+        if rc != DVR_OK:
+            raise DvrError(rc, self.last_error())
+
+    # -- the four entry points -------------------------------------------------------------
+    def render_forward(self, inputs: Inputs, color, termination_index, stream: int = 0):
+        ci, co = inputs.to_c(), make_outputs(color, termination_index)
+        self._check(getattr(self.lib, self.prefix + "render_forward")(ci, co, stream))
+
+    def render_forward_gradients(self, inputs: Inputs, settings: DvrForwardDifferencesSettings,
+                                 color, termination_index, gradients_out, stream: int = 0):
+        ci, co, g = inputs.to_c(), make_outputs(color, termination_index), tensor_view(gradients_out)
+        self._check(getattr(self.lib, self.prefix + "render_forward_gradients")(ci, settings, co, g,
+                                                                               stream))
+
+    def forward_variables_to_gradients(self, forward_variables, grad_output_color,
+                                       settings: DvrForwardDifferencesSettings,
+                                       adj: DvrAdjointOutputs, stream: int = 0):
+        fv, gc = tensor_view(forward_variables), tensor_view(grad_output_color)
+        self._check(getattr(self.lib, self.prefix + "forward_variables_to_gradients")(
+            fv, gc, settings, adj, stream))
+
+    def render_adjoint(self, inputs: Inputs, color, termination_index, adj_color,
+                       adj: DvrAdjointOutputs, stream: int = 0):
+        ci, co, ac = inputs.to_c(), make_outputs(color, termination_index), tensor_view(adj_color)
+        self._check(getattr(self.lib, self.prefix + "render_adjoint")(ci, co, ac, adj, stream))
+
+
+_PRODUCT: Optional["ProductLibrary"] = None
+
+
+class ProductLibrary(Library):
+    """``libdvr_b200.so`` -- the CUDA product library (device pointers, CUDA streams)."""
+
+    def __init__(self, path: str):
+        super().__init__(path, "dvr_")
+        L = self.lib
+        L.dvr_set_option.restype = ctypes.c_int
+        L.dvr_set_option.argtypes = [ctypes.c_char_p, ctypes.c_int32]
+        L.dvr_get_option.restype = ctypes.c_int
+        L.dvr_get_option.argtypes = [ctypes.c_char_p, ctypes.POINTER(ctypes.c_int32)]
+        L.dvr_launch_count.restype = ctypes.c_int64
+        L.dvr_launch_count.argtypes = []
+        L.dvr_has_variant.restype = ctypes.c_int
+        L.dvr_has_variant.argtypes = [ctypes.c_int32] * 4
+        L.dvr_abi_version.restype = ctypes.c_int32
+        L.dvr_abi_version.argtypes = []
+        L.dvr_check_inputs.restype = ctypes.c_int
+        L.dvr_check_inputs.argtypes = [ctypes.POINTER(DvrInputs)] + [ctypes.POINTER(ctypes.c_int32)] * 4
+
+    def set_option(self, name: str, value: int):
+        self._check(self.lib.dvr_set_option(name.encode(), int(value)))
+
+    def get_option(self, name: str) -> int:
+        v = ctypes.c_int32()
+        self._check(self.lib.dvr_get_option(name.encode(), ctypes.byref(v)))
+        return v.value
+
+    def launch_count(self) -> int:
+        return int(self.lib.dvr_launch_count())
+
+    def has_variant(self, filter_mode, camera_mode, tf_mode, blend_mode) -> bool:
+        return bool(self.lib.dvr_has_variant(filter_mode, camera_mode, tf_mode, blend_mode))
+
+    def check_inputs(self, inputs: Inputs):
+        B, X, Y, Z = (ctypes.c_int32() for _ in range(4))
+        ci = inputs.to_c()
+        self._check(self.lib.dvr_check_inputs(ci, ctypes.byref(B), ctypes.byref(X), ctypes.byref(Y),
+                                              ctypes.byref(Z)))
+        return B.value, X.value, Y.value, Z.value
+
+
+def library_path() -> str:
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "libdvr_b200.so")
+
+
+def load() -> ProductLibrary:
+    """Loads the CUDA library; raises (loudly) if it has not been built -- no fallback."""
+    global _PRODUCT
+    if _PRODUCT is None:
+        path = library_path()
+        if not os.path.exists(path):
+            raise RuntimeError(
+                f"{path} not found: the CUDA extension is not built (run "
+                "`python -c 'import __graft_entry__ as g; g.build()'`); there is no CPU fallback")
+        _PRODUCT = ProductLibrary(path)
+    return _PRODUCT

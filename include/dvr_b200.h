@@ -1,0 +1,208 @@
+/*
+ * dvr_b200.h -- C-ABI of the B200-native differentiable volume ray marcher.
+ *
+ * Drop-in boundary for ONE hot path of shamanDevel/DiffDVR: the three data-parallel
+ * kernels of renderer/renderer_kernels.cuh (plain forward, forward-mode derivatives,
+ * adjoint) plus the forward-variables -> gradients reduction.
+ *
+ * Every entry point below replaces one method of the reference's CUDA back-end
+ * `renderer::RendererCuda` (renderer/renderer_cuda.h:34-123), which in the reference
+ * assembles a template name, NVRTC-compiles it (renderer/kernel_loader.cpp:193-261) and
+ * calls cuLaunchKernel (renderer/renderer_cuda.cpp:85-118,120-183,185-224,226-317).
+ * Here the variants are precompiled sm_100a instances behind a static dispatch table.
+ *
+ * Conventions
+ *  - plain C, no torch types; all pointers are DEVICE pointers (fp32 / int32);
+ *  - a tensor is {ptr, ndim, size[], stride[]} with strides in ELEMENTS (like torch);
+ *    a leading/any dimension of size 1 broadcasts (stride forced to 0), exactly like the
+ *    reference's BroadcastingTensorAccessor (renderer/renderer_tensor.cuh:140-144);
+ *  - enums are int32 with the reference's numeric values
+ *    (renderer/renderer_settings.cuh:81-146);
+ *  - adjoint outputs are ACCUMULATED into caller-zeroed tensors
+ *    (renderer/renderer_settings.cuh:227-229);
+ *  - every function returns DVR_OK (0) or a negative error code, never throws;
+ *    dvr_last_error() returns a thread-local message for the last failure;
+ *  - launches are asynchronous on `stream` (a cudaStream_t passed as void*), like the
+ *    reference's launches on the current torch stream (renderer/renderer_cuda.cpp:105).
+ */
+#ifndef DVR_B200_H
+#define DVR_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DVR_MAX_DIMS 5
+
+/* error codes */
+#define DVR_OK 0
+#define DVR_ERR_INVALID_ARGUMENT (-1) /* shape / enum / flag validation failed      */
+#define DVR_ERR_UNSUPPORTED (-2)      /* variant not compiled (see dvr_has_variant) */
+#define DVR_ERR_CUDA (-3)             /* CUDA runtime reported an error             */
+
+/* renderer/renderer_settings.cuh:81-90 */
+enum DvrVolumeFilterMode {
+  DVR_FILTER_NEAREST = 0,
+  DVR_FILTER_TRILINEAR = 1,
+  DVR_FILTER_PRESHADED = 3, /* volume holds RGBA in the batch dimension */
+  DVR_FILTER_NETWORK = 4    /* not supported (scene networks are off the path) */
+};
+/* renderer/renderer_settings.cuh:92-126 */
+enum DvrCameraMode {
+  DVR_CAMERA_RAY_START_DIR = 0,       /* per-pixel rays  (B)*H*W*3 twice   */
+  DVR_CAMERA_INVERSE_VIEW_MATRIX = 1, /* (B)*4*4 inverse view-projection   */
+  DVR_CAMERA_REFERENCE_FRAME = 2      /* (B)*3*3 eye/right/up + fovY       */
+};
+/* renderer/renderer_settings.cuh:128-139 */
+enum DvrTFMode {
+  DVR_TF_IDENTITY = 0,    /* (B)*1*2 */
+  DVR_TF_TEXTURE = 1,     /* (B)*R*4 */
+  DVR_TF_LINEAR = 2,      /* (B)*R*5 */
+  DVR_TF_GAUSSIAN = 3,    /* (B)*R*6 */
+  DVR_TF_PRESHADED = 5,   /* TF ignored */
+  DVR_TF_GAUSSIAN_LOG = 6 /* (B)*R*6, returns log-space colours */
+};
+/* renderer/renderer_settings.cuh:141-146 */
+enum DvrBlendMode { DVR_BLEND_BEER_LAMBERT = 0, DVR_BLEND_ALPHA = 1 };
+
+/* Strided tensor view; replaces kernel::GenericPackedTensorAccessor
+ * (renderer/renderer_tensor.cuh:122-269). ptr == NULL means "not provided". */
+typedef struct DvrTensor {
+  void* ptr;
+  int32_t ndim;
+  int64_t size[DVR_MAX_DIMS];
+  int64_t stride[DVR_MAX_DIMS]; /* in elements */
+} DvrTensor;
+
+/* Replaces renderer::RendererInputsHost (renderer/renderer.h:20-64) and
+ * kernel::RendererInputs (renderer/renderer_settings.cuh:150-180).
+ * Scalar variants of the host struct are passed BY VALUE: when the tensor's ptr is NULL
+ * the *_value field next to it is used (no temporary tensor, no H2D copy; the reference
+ * uploads a 1-element tensor per call, renderer/renderer.cpp:101-102,117-118,217-218). */
+typedef struct DvrInputs {
+  int32_t screen_width;  /* W */
+  int32_t screen_height; /* H */
+
+  int32_t volume_filter_mode; /* DvrVolumeFilterMode */
+  DvrTensor volume;           /* (B)*X*Y*Z fp32, any strides (4*X*Y*Z in preshaded mode) */
+
+  DvrTensor box_min;  /* (B)*3 */
+  float box_min_value[3];
+  DvrTensor box_size; /* (B)*3 */
+  float box_size_value[3];
+
+  int32_t camera_mode;         /* DvrCameraMode */
+  DvrTensor camera_ray_start;  /* (B)*H*W*3, mode RAY_START_DIR */
+  DvrTensor camera_ray_dir;    /* (B)*H*W*3, mode RAY_START_DIR */
+  DvrTensor camera_matrix;     /* (B)*4*4 (INVERSE_VIEW_MATRIX) or (B)*3*3 (REFERENCE_FRAME) */
+  float camera_matrix_value[16]; /* row-major 4*4 used when camera_matrix.ptr==NULL in
+                                    INVERSE_VIEW_MATRIX mode (the glm::mat4 variant) */
+  float camera_fov_y_radians;  /* mode REFERENCE_FRAME */
+
+  DvrTensor step_size; /* (B)*(H)*(W) */
+  float step_size_value;
+
+  int32_t tf_mode; /* DvrTFMode */
+  DvrTensor tf;    /* (B)*R*C */
+
+  int32_t blend_mode;       /* DvrBlendMode */
+  float blending_early_out; /* reference default: 1 - 1e-5 */
+} DvrInputs;
+
+/* Replaces renderer::RendererOutputsHost (renderer/renderer.h:67-71). */
+typedef struct DvrOutputs {
+  DvrTensor color;             /* B*H*W*4 fp32 */
+  DvrTensor termination_index; /* B*H*W   int32 */
+} DvrOutputs;
+
+/* Replaces renderer::ForwardDifferencesSettingsHost (renderer/renderer.h:74-93). */
+typedef struct DvrForwardDifferencesSettings {
+  int32_t D;              /* number of traced derivatives */
+  int32_t d_stepsize;     /* derivative slot or -1 */
+  int32_t d_ray_start[3]; /* derivative slots or -1 */
+  int32_t d_ray_dir[3];   /* derivative slots or -1 */
+  DvrTensor d_tf;         /* (B)*R*C int32 slots or -1; may be NULL if !has_tf_derivatives */
+  int32_t has_tf_derivatives;
+} DvrForwardDifferencesSettings;
+
+/* Replaces renderer::AdjointOutputsHost (renderer/renderer.h:95-111). */
+typedef struct DvrAdjointOutputs {
+  int32_t has_volume_derivatives;
+  DvrTensor adj_volume; /* (B)*X*Y*Z */
+  int32_t has_stepsize_derivatives;
+  DvrTensor adj_step_size; /* (B)*(H)*(W) */
+  int32_t has_camera_derivatives;
+  DvrTensor adj_camera_ray_start; /* (B)*H*W*3 */
+  DvrTensor adj_camera_ray_dir;   /* (B)*H*W*3 */
+  int32_t has_tf_derivatives;
+  int32_t tf_delayed_accumulation; /* accepted for API parity; both settings give the same result */
+  DvrTensor adj_tf;                /* (B)*R*C */
+} DvrAdjointOutputs;
+
+/* RendererCuda::renderForward (renderer/renderer_cuda.cpp:85-118) ->
+ * DvrKernelForwardDevice (renderer/renderer_kernels.cuh:92-106). */
+int dvr_render_forward(const DvrInputs* inputs, const DvrOutputs* outputs, void* stream);
+
+/* RendererCuda::renderForwardGradients (renderer/renderer_cuda.cpp:120-183) ->
+ * DvrKernelForwardGradientsDevice (renderer/renderer_kernels.cuh:258-279).
+ * gradients_out: B*H*W*D*4 fp32. */
+int dvr_render_forward_gradients(const DvrInputs* inputs,
+                                 const DvrForwardDifferencesSettings* settings,
+                                 const DvrOutputs* outputs, const DvrTensor* gradients_out,
+                                 void* stream);
+
+/* RendererCuda::forwardVariablesToGradients (renderer/renderer_cuda.cpp:185-224) ->
+ * ForwardVariablesToGradientsDevice (renderer/renderer_kernels.cuh:564-576). */
+int dvr_forward_variables_to_gradients(const DvrTensor* forward_variables,
+                                       const DvrTensor* grad_output_color,
+                                       const DvrForwardDifferencesSettings* settings,
+                                       const DvrAdjointOutputs* adj_outputs, void* stream);
+
+/* RendererCuda::renderAdjoint (renderer/renderer_cuda.cpp:226-317) ->
+ * DvrKernelAdjointDevice (renderer/renderer_kernels.cuh:447-468). */
+int dvr_render_adjoint(const DvrInputs* inputs, const DvrOutputs* outputs_from_forward,
+                       const DvrTensor* adj_color, const DvrAdjointOutputs* adj_outputs,
+                       void* stream);
+
+/* Computes the broadcast batch size and volume resolution exactly like
+ * Renderer::checkInputs (renderer/renderer.cpp:49-263); validates shapes.
+ * Any out pointer may be NULL. */
+int dvr_check_inputs(const DvrInputs* inputs, int32_t* B, int32_t* X, int32_t* Y, int32_t* Z);
+
+/* 1 if the (filter, camera, tf, blend) combination has a precompiled instance, else 0.
+ * Replaces "does it compile under NVRTC" (unittests/testCudaCompilation.cpp:109-287). */
+int dvr_has_variant(int32_t volume_filter_mode, int32_t camera_mode, int32_t tf_mode,
+                    int32_t blend_mode);
+
+/* Runtime options (replace Renderer::setCudaSyncMode etc., renderer/renderer.h:128-150,
+ * and the compile-time switches of the reference):
+ *   "sync_mode"                 0/1  cudaStreamSynchronize after every launch (default 0)
+ *   "compat_stepsize_overwrite" 0/1  1 reproduces the reference's adjoint stepsize
+ *                                    recurrence bit-for-bit (the blend term of the stepsize
+ *                                    adjoint is overwritten every sample,
+ *                                    renderer/renderer_kernels.cuh:393-395 with
+ *                                    renderer/renderer_blending.cuh:93,158); 0 (default)
+ *                                    accumulates it (mathematically complete gradient).
+ *   "volume_layout"             0 = sample the caller's strided tensor directly,
+ *                               1 = re-brick into the internal tiled layout per call,
+ *                               -1 (default) = automatic
+ * Returns DVR_OK or DVR_ERR_INVALID_ARGUMENT for an unknown name. */
+int dvr_set_option(const char* name, int32_t value);
+int dvr_get_option(const char* name, int32_t* value);
+
+/* Number of kernel launches issued by this library since load (for bench accounting). */
+int64_t dvr_launch_count(void);
+
+/* Thread-local description of the last error returned on this thread ("" if none). */
+const char* dvr_last_error(void);
+
+/* ABI version of this header. */
+int32_t dvr_abi_version(void);
+#define DVR_ABI_VERSION 1
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DVR_B200_H */
