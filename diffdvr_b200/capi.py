@@ -293,6 +293,9 @@ class ProductLibrary(Library):
         L.dvr_has_variant.argtypes = [ctypes.c_int32] * 4
         L.dvr_abi_version.restype = ctypes.c_int32
         L.dvr_abi_version.argtypes = []
+        L.dvr_count_cell_visits.restype = ctypes.c_int
+        L.dvr_count_cell_visits.argtypes = [ctypes.POINTER(DvrInputs), ctypes.POINTER(DvrTensor), ctypes.c_void_p,
+                                            ctypes.c_void_p]
         L.dvr_check_inputs.restype = ctypes.c_int
         L.dvr_check_inputs.argtypes = [ctypes.POINTER(DvrInputs)] + [ctypes.POINTER(ctypes.c_int32)] * 4
 
@@ -309,6 +312,11 @@ class ProductLibrary(Library):
 
     def has_variant(self, filter_mode, camera_mode, tf_mode, blend_mode) -> bool:
         return bool(self.lib.dvr_has_variant(filter_mode, camera_mode, tf_mode, blend_mode))
+
+    def count_cell_visits(self, inputs: Inputs, termination_index, counts, stream: int = 0):
+        """counts: device tensor of 2 int64 {N_samples, N_cells}, accumulated."""
+        ci, t = inputs.to_c(), tensor_view(termination_index)
+        self._check(self.lib.dvr_count_cell_visits(ci, t, counts.data_ptr(), stream))
 
     def check_inputs(self, inputs: Inputs):
         B, X, Y, Z = (ctypes.c_int32() for _ in range(4))

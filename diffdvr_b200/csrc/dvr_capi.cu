@@ -1,0 +1,589 @@
+// C-ABI of the B200 ray marcher (include/dvr_b200.h): validation, stride resolution and
+// dispatch to the precompiled kernel instances. Plays the role of Renderer::checkInputs /
+// checkOutput / checkAdjointOutput (renderer/renderer.cpp:49-391) for shapes and of
+// RendererCuda (renderer/renderer_cuda.cpp:85-317) for launching. No torch types, no device
+// allocations, no host<->device copies, no CPU fallback.
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/dvr_b200.h"
+#include "dvr_launch.h"
+#include "dvr_kernels.cuh"  // kRegRows, TfLayout, TfChannels (host-side constants only)
+
+namespace {
+
+using namespace dvr;
+
+thread_local std::string g_error;
+std::atomic<long long> g_launches{0};
+std::atomic<int> g_sync_mode{0};
+std::atomic<int> g_compat_stepsize{0};
+std::atomic<int> g_volume_layout{-1};
+
+struct Fail {
+  int code;
+};
+
+[[noreturn]] void fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_error = buf;
+  throw Fail{code};
+}
+
+template <typename F>
+int guarded(F&& f) {
+  try {
+    f();
+    return DVR_OK;
+  } catch (const Fail& e) {
+    return e.code;
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return DVR_ERR_INVALID_ARGUMENT;
+  }
+}
+
+void cuda_check(cudaError_t e, const char* what) {
+  if (e == cudaErrorInvalidValue) fail(DVR_ERR_UNSUPPORTED, "%s: no precompiled kernel instance for this combination", what);
+  if (e != cudaSuccess) fail(DVR_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+
+void after_launch(cudaError_t e, const char* what, cudaStream_t s) {
+  cuda_check(e, what);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  if (g_sync_mode.load()) cuda_check(cudaStreamSynchronize(s), what);  // Renderer::setCudaSyncMode
+}
+
+// ---- shape checks, with the reference's wording (renderer/pytorch_utils.h:5-19) ---------------
+void check_dim(const DvrTensor& t, const char* name, int d) {
+  if (!t.ptr) fail(DVR_ERR_INVALID_ARGUMENT, "%s is not defined!", name);
+  if (t.ndim != d) fail(DVR_ERR_INVALID_ARGUMENT, "%s must be a tensor with %d dimensions, but has %d", name, d, t.ndim);
+}
+void check_size(const DvrTensor& t, const char* name, int d, long long s) {
+  if (t.size[d] != s)
+    fail(DVR_ERR_INVALID_ARGUMENT, "%s must have %lld entries at dimension %d, but has %lld entries", name, s, d,
+         (long long)t.size[d]);
+}
+int check_batch(const DvrTensor& t, const char* name, int B1, int dim = 0) {
+  const int B2 = int(t.size[dim]);
+  if (B2 == 1) return B1;
+  if (B1 == 1) return B2;
+  if (B1 != B2)
+    fail(DVR_ERR_INVALID_ARGUMENT, "%s must be have the same batch size as other tensors, if batch>1. actual=%d, expected=%d",
+         name, B2, B1);
+  return B1;
+}
+long long bstride(const DvrTensor& t, int d) { return t.size[d] == 1 ? 0 : t.stride[d]; }
+
+struct Checked {
+  int B = 1, W = 0, H = 0, X = 0, Y = 0, Z = 0;
+  RayInputs ri;
+};
+
+// Renderer::checkInputs (renderer/renderer.cpp:49-263)
+void check_inputs(const DvrInputs& a, Checked& c) {
+  RayInputs& r = c.ri;
+  std::memset(&r, 0, sizeof(r));
+  c.W = a.screen_width;
+  c.H = a.screen_height;
+  if (c.W <= 0 || c.H <= 0) fail(DVR_ERR_INVALID_ARGUMENT, "screenSize must be positive, but is (%d, %d)", c.W, c.H);
+  check_dim(a.volume, "volume", 4);
+  const bool preshaded = a.volume_filter_mode == DVR_FILTER_PRESHADED;
+  if (preshaded != (a.tf_mode == DVR_TF_PRESHADED))
+    fail(DVR_ERR_INVALID_ARGUMENT, "if pre-shading is selected, both the filter mode and TF mode must be set to preshaded");
+  if (preshaded) fail(DVR_ERR_UNSUPPORTED, "pre-shaded volumes (FilterPreshaded/TFPreshaded) have no sm_100a instance yet");
+  if (a.volume_filter_mode != DVR_FILTER_NEAREST && a.volume_filter_mode != DVR_FILTER_TRILINEAR)
+    fail(DVR_ERR_UNSUPPORTED, "volume filter mode %d is not supported", a.volume_filter_mode);
+  int B = int(a.volume.size[0]);
+  c.X = int(a.volume.size[1]);
+  c.Y = int(a.volume.size[2]);
+  c.Z = int(a.volume.size[3]);
+  if (c.X < 1 || c.Y < 1 || c.Z < 1) fail(DVR_ERR_INVALID_ARGUMENT, "volume must not be empty");
+  {
+    long long span = 0;
+    for (int d = 1; d < 4; ++d) span += (a.volume.size[d] - 1) * bstride(a.volume, d);
+    if (span >= (1ll << 31) || c.X >= (1 << 22) || c.Y >= (1 << 22) || c.Z >= (1 << 22))
+      fail(DVR_ERR_UNSUPPORTED, "one volume batch entry must span fewer than 2^31 elements");
+  }
+  r.volume = static_cast<const float*>(a.volume.ptr);
+  r.volB = bstride(a.volume, 0);
+  r.sx = int(bstride(a.volume, 1));
+  r.sy = int(bstride(a.volume, 2));
+  r.sz = int(bstride(a.volume, 3));
+  r.X = c.X; r.Y = c.Y; r.Z = c.Z;
+
+  if (a.box_min.ptr) {
+    check_dim(a.box_min, "boxMin", 2);
+    check_size(a.box_min, "boxMin", 1, 3);
+    B = check_batch(a.box_min, "boxMin", B);
+    r.boxMin = {static_cast<const float*>(a.box_min.ptr), bstride(a.box_min, 0), a.box_min.stride[1]};
+  } else {
+    for (int i = 0; i < 3; ++i) r.boxMinV[i] = a.box_min_value[i];
+  }
+  if (a.box_size.ptr) {
+    check_dim(a.box_size, "boxSize", 2);
+    check_size(a.box_size, "boxSize", 1, 3);
+    B = check_batch(a.box_size, "boxSize", B);
+    r.boxSize = {static_cast<const float*>(a.box_size.ptr), bstride(a.box_size, 0), a.box_size.stride[1]};
+  } else {
+    for (int i = 0; i < 3; ++i) r.boxSizeV[i] = a.box_size_value[i];
+  }
+
+  r.cameraMode = a.camera_mode;
+  switch (a.camera_mode) {
+    case DVR_CAMERA_RAY_START_DIR: {
+      const DvrTensor* ts[2] = {&a.camera_ray_start, &a.camera_ray_dir};
+      const char* names[2] = {"cameraRayStart", "cameraRayDir"};
+      Strided4* dst[2] = {&r.rayStart, &r.rayDir};
+      for (int k = 0; k < 2; ++k) {
+        check_dim(*ts[k], names[k], 4);
+        check_size(*ts[k], names[k], 1, c.H);
+        check_size(*ts[k], names[k], 2, c.W);
+        check_size(*ts[k], names[k], 3, 3);
+        B = check_batch(*ts[k], names[k], B);
+        *dst[k] = {static_cast<const float*>(ts[k]->ptr), bstride(*ts[k], 0), bstride(*ts[k], 1), bstride(*ts[k], 2),
+                   ts[k]->stride[3]};
+      }
+    } break;
+    case DVR_CAMERA_INVERSE_VIEW_MATRIX:
+      if (a.camera_matrix.ptr) {
+        check_dim(a.camera_matrix, "cameraMatrix", 3);
+        check_size(a.camera_matrix, "cameraMatrix", 1, 4);
+        check_size(a.camera_matrix, "cameraMatrix", 2, 4);
+        B = check_batch(a.camera_matrix, "cameraMatrix", B);
+        r.camMat = {static_cast<const float*>(a.camera_matrix.ptr), bstride(a.camera_matrix, 0),
+                    a.camera_matrix.stride[1], a.camera_matrix.stride[2]};
+      } else {
+        for (int i = 0; i < 16; ++i) r.camMatV[i] = a.camera_matrix_value[i];
+      }
+      break;
+    case DVR_CAMERA_REFERENCE_FRAME: {
+      check_dim(a.camera_matrix, "cameraMatrix", 3);
+      check_size(a.camera_matrix, "cameraMatrix", 1, 3);
+      check_size(a.camera_matrix, "cameraMatrix", 2, 3);
+      B = check_batch(a.camera_matrix, "cameraMatrix", B);
+      r.camMat = {static_cast<const float*>(a.camera_matrix.ptr), bstride(a.camera_matrix, 0),
+                  a.camera_matrix.stride[1], a.camera_matrix.stride[2]};
+      // renderer_camera.cuh:42-45: the ANGLE is scaled by the aspect ratio, then halved
+      const float fovX = a.camera_fov_y_radians * float(c.W) / float(c.H);
+      r.tanFovX = std::tan(fovX / 2);
+      r.tanFovY = std::tan(a.camera_fov_y_radians / 2);
+    } break;
+    default: fail(DVR_ERR_INVALID_ARGUMENT, "unknown camera enum value");
+  }
+
+  if (a.step_size.ptr) {
+    check_dim(a.step_size, "stepSize", 3);
+    B = check_batch(a.step_size, "stepSize", B);
+    check_batch(a.step_size, "stepSize-Height", c.H, 1);
+    check_batch(a.step_size, "stepSize-Width", c.W, 2);
+    r.stepSize = {static_cast<const float*>(a.step_size.ptr), bstride(a.step_size, 0), bstride(a.step_size, 1),
+                  bstride(a.step_size, 2)};
+  } else {
+    r.stepV = a.step_size_value;
+  }
+
+  check_dim(a.tf, "tf", 3);
+  B = check_batch(a.tf, "tf", B);
+  switch (a.tf_mode) {
+    case DVR_TF_IDENTITY:
+      check_size(a.tf, "tf", 1, 1);
+      check_size(a.tf, "tf", 2, 2);
+      break;
+    case DVR_TF_TEXTURE: check_size(a.tf, "tf", 2, 4); break;
+    case DVR_TF_LINEAR:
+      check_size(a.tf, "tf", 2, 5);
+      if (a.tf.size[1] <= 1)
+        fail(DVR_ERR_INVALID_ARGUMENT, "tensor 'tf' must have at least two control points in TFLinear-mode");
+      break;
+    case DVR_TF_GAUSSIAN:
+    case DVR_TF_GAUSSIAN_LOG: check_size(a.tf, "tf", 2, 6); break;
+    default: fail(DVR_ERR_INVALID_ARGUMENT, "unknown tf enum value");
+  }
+  if (a.tf.size[1] < 1) fail(DVR_ERR_INVALID_ARGUMENT, "tensor 'tf' must have at least one row");
+  r.tf = {static_cast<const float*>(a.tf.ptr), bstride(a.tf, 0), a.tf.stride[1], a.tf.stride[2]};
+  r.R = int(a.tf.size[1]);
+  r.C = int(a.tf.size[2]);
+  if (a.blend_mode != DVR_BLEND_BEER_LAMBERT && a.blend_mode != DVR_BLEND_ALPHA)
+    fail(DVR_ERR_INVALID_ARGUMENT, "unknown blend mode");
+  r.earlyOut = a.blending_early_out;
+  if (B > 65535) fail(DVR_ERR_UNSUPPORTED, "batch size %d exceeds 65535", B);
+  c.B = B;
+  r.W = c.W; r.H = c.H; r.B = B;
+}
+
+// Renderer::checkOutput (renderer/renderer.cpp:367-391)
+ForwardOutputs check_outputs(const DvrOutputs& o, const Checked& c) {
+  check_dim(o.color, "color", 4);
+  check_size(o.color, "color", 0, c.B);
+  check_size(o.color, "color", 1, c.H);
+  check_size(o.color, "color", 2, c.W);
+  check_size(o.color, "color", 3, 4);
+  check_dim(o.termination_index, "terminationIndex", 3);
+  check_size(o.termination_index, "terminationIndex", 0, c.B);
+  check_size(o.termination_index, "terminationIndex", 1, c.H);
+  check_size(o.termination_index, "terminationIndex", 2, c.W);
+  ForwardOutputs f;
+  f.color = static_cast<float*>(o.color.ptr);
+  f.cB = o.color.stride[0]; f.cY = o.color.stride[1]; f.cX = o.color.stride[2]; f.cC = o.color.stride[3];
+  f.colorVec4 = f.cC == 1 && (reinterpret_cast<uintptr_t>(f.color) % 16 == 0) && f.cB % 4 == 0 && f.cY % 4 == 0 &&
+                f.cX % 4 == 0;
+  f.term = static_cast<int*>(o.termination_index.ptr);
+  f.tB = o.termination_index.stride[0]; f.tY = o.termination_index.stride[1]; f.tX = o.termination_index.stride[2];
+  return f;
+}
+
+dim3 tile_grid(const Checked& c) {
+  return dim3((c.W + kCtaW - 1) / kCtaW, (c.H + kCtaH - 1) / kCtaH, c.B);
+}
+
+template <int TFMODE> constexpr int row_of() { return TfLayout<TFMODE>::kRow; }
+int tf_row(int tf) { return tf == kTfIdentity ? 2 : tf == kTfTexture ? 4 : 8; }
+int tf_channels(int tf) { return tf == kTfIdentity ? 2 : tf == kTfTexture ? 4 : tf == kTfLinear ? 5 : 6; }
+size_t check_smem(size_t bytes) {
+  if (bytes > 200 * 1024) fail(DVR_ERR_UNSUPPORTED, "transfer function too large for shared memory (%zu bytes)", bytes);
+  return bytes;
+}
+
+// checkAdjointOutput (renderer/renderer.cpp:265-365); X<0 skips the volume checks
+void check_adjoint_outputs(const DvrAdjointOutputs& o, int B, int H, int W, int X, int Y, int Z, const DvrTensor* tf,
+                           AdjointArgs& aa) {
+  if (o.has_volume_derivatives) {
+    check_dim(o.adj_volume, "adj_volume", 4);
+    check_batch(o.adj_volume, "adj_volume", B);
+    check_size(o.adj_volume, "adj_volume", 1, X);
+    check_size(o.adj_volume, "adj_volume", 2, Y);
+    check_size(o.adj_volume, "adj_volume", 3, Z);
+    long long span = 0;
+    for (int d = 1; d < 4; ++d) span += (o.adj_volume.size[d] - 1) * bstride(o.adj_volume, d);
+    if (span >= (1ll << 31)) fail(DVR_ERR_UNSUPPORTED, "one adj_volume batch entry must span fewer than 2^31 elements");
+    aa.adjVolume = static_cast<float*>(o.adj_volume.ptr);
+    aa.avB = bstride(o.adj_volume, 0);
+    aa.avx = int(bstride(o.adj_volume, 1));
+    aa.avy = int(bstride(o.adj_volume, 2));
+    aa.avz = int(bstride(o.adj_volume, 3));
+  }
+  aa.hasStep = o.has_stepsize_derivatives != 0;
+  if (aa.hasStep) {
+    check_dim(o.adj_step_size, "adj_stepSize", 3);
+    check_batch(o.adj_step_size, "adj_stepSize", B);
+    check_batch(o.adj_step_size, "adj_stepSize", H, 1);
+    check_batch(o.adj_step_size, "adj_stepSize", W, 2);
+    aa.adjStep = static_cast<float*>(o.adj_step_size.ptr);
+    aa.asB = bstride(o.adj_step_size, 0); aa.asY = bstride(o.adj_step_size, 1); aa.asX = bstride(o.adj_step_size, 2);
+    aa.stepAtomic = B != o.adj_step_size.size[0] || H != o.adj_step_size.size[1] || W != o.adj_step_size.size[2];
+  }
+  aa.hasCam = o.has_camera_derivatives != 0;
+  if (aa.hasCam) {
+    const DvrTensor* ts[2] = {&o.adj_camera_ray_start, &o.adj_camera_ray_dir};
+    const char* names[2] = {"adj_cameraRayStart", "adj_cameraRayDir"};
+    for (int k = 0; k < 2; ++k) {
+      check_dim(*ts[k], names[k], 4);
+      check_batch(*ts[k], names[k], B);
+      check_size(*ts[k], names[k], 1, H);
+      check_size(*ts[k], names[k], 2, W);
+      check_size(*ts[k], names[k], 3, 3);
+    }
+    aa.adjRayStart = static_cast<float*>(ts[0]->ptr);
+    aa.rsB = bstride(*ts[0], 0); aa.rsY = bstride(*ts[0], 1); aa.rsX = bstride(*ts[0], 2); aa.rsC = ts[0]->stride[3];
+    aa.adjRayDir = static_cast<float*>(ts[1]->ptr);
+    aa.rdB = bstride(*ts[1], 0); aa.rdY = bstride(*ts[1], 1); aa.rdX = bstride(*ts[1], 2); aa.rdC = ts[1]->stride[3];
+    aa.camAtomic = B != ts[0]->size[0] || B != ts[1]->size[0];
+  }
+  if (o.has_tf_derivatives) {
+    check_dim(o.adj_tf, "adj_tf", 3);
+    check_batch(o.adj_tf, "adj_tf", B);
+    if (tf) {
+      check_size(o.adj_tf, "adj_tf", 1, tf->size[1]);
+      check_size(o.adj_tf, "adj_tf", 2, tf->size[2]);
+    }
+    aa.adjTf = static_cast<float*>(o.adj_tf.ptr);
+    aa.atB = bstride(o.adj_tf, 0); aa.atR = o.adj_tf.stride[1]; aa.atC = o.adj_tf.stride[2];
+  }
+}
+
+Strided4 strided4(const DvrTensor& t) {
+  return {static_cast<const float*>(t.ptr), bstride(t, 0), bstride(t, 1), bstride(t, 2), t.stride[3]};
+}
+
+void fill_fd_settings(const DvrForwardDifferencesSettings& s, int* dStep, int* dStart, int* dDir) {
+  *dStep = s.d_stepsize;
+  for (int i = 0; i < 3; ++i) {
+    dStart[i] = s.d_ray_start[i];
+    dDir[i] = s.d_ray_dir[i];
+  }
+}
+
+}  // namespace
+
+namespace dvr {
+
+cudaError_t launch_adjoint(int filter, int tf, int blend, bool hasVol, int tfacc, bool hasRay, const RayInputs& in,
+                           const AdjointArgs& aa, dim3 grid, size_t smem, cudaStream_t s) {
+#define DVR_CASE(TF, BL) \
+  if (tf == TF && blend == BL) return launch_adjoint_##TF##_##BL(filter, hasVol, tfacc, hasRay, in, aa, grid, smem, s);
+  DVR_CASE(0, 0) DVR_CASE(0, 1) DVR_CASE(1, 0) DVR_CASE(1, 1) DVR_CASE(2, 0) DVR_CASE(2, 1) DVR_CASE(3, 0)
+  DVR_CASE(3, 1) DVR_CASE(6, 0) DVR_CASE(6, 1)
+#undef DVR_CASE
+  return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_forward_gradients(int filter, int tf, int blend, int chunk, bool hasPos, bool hasTf,
+                                     const RayInputs& in, const ForwardOutputs& out, const ForwardGradArgs& ga,
+                                     dim3 grid, size_t smem, cudaStream_t s) {
+#define DVR_CASE(TF, BL) \
+  if (tf == TF && blend == BL) return launch_fwdgrad_##TF##_##BL(filter, chunk, hasPos, hasTf, in, out, ga, grid, smem, s);
+  DVR_CASE(0, 0) DVR_CASE(0, 1) DVR_CASE(1, 0) DVR_CASE(1, 1) DVR_CASE(2, 0) DVR_CASE(2, 1) DVR_CASE(3, 0)
+  DVR_CASE(3, 1)
+#undef DVR_CASE
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace dvr
+
+// ================================================================================================
+extern "C" {
+
+int dvr_check_inputs(const DvrInputs* inputs, int32_t* B, int32_t* X, int32_t* Y, int32_t* Z) {
+  return guarded([&] {
+    if (!inputs) fail(DVR_ERR_INVALID_ARGUMENT, "inputs is NULL");
+    Checked c;
+    check_inputs(*inputs, c);
+    if (B) *B = c.B;
+    if (X) *X = c.X;
+    if (Y) *Y = c.Y;
+    if (Z) *Z = c.Z;
+  });
+}
+
+int dvr_render_forward(const DvrInputs* inputs, const DvrOutputs* outputs, void* stream) {
+  return guarded([&] {
+    if (!inputs || !outputs) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    Checked c;
+    check_inputs(*inputs, c);
+    const ForwardOutputs fo = check_outputs(*outputs, c);
+    const size_t smem = check_smem(size_t(c.ri.R) * tf_row(inputs->tf_mode) * sizeof(float));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    after_launch(launch_forward(inputs->volume_filter_mode, inputs->tf_mode, inputs->blend_mode, c.ri, fo,
+                                tile_grid(c), smem, s),
+                 "dvr_render_forward", s);
+  });
+}
+
+int dvr_render_adjoint(const DvrInputs* inputs, const DvrOutputs* fwd, const DvrTensor* adj_color,
+                       const DvrAdjointOutputs* adj, void* stream) {
+  return guarded([&] {
+    if (!inputs || !fwd || !adj_color || !adj) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    Checked c;
+    check_inputs(*inputs, c);
+    // outputs of the forward pass (renderer.cpp:670-691) and adjoint colour (:693-701)
+    const DvrTensor* col[2] = {&fwd->color, adj_color};
+    const char* names[2] = {"output_color", "adj_color"};
+    for (int k = 0; k < 2; ++k) {
+      check_dim(*col[k], names[k], 4);
+      check_size(*col[k], names[k], 0, c.B);
+      check_size(*col[k], names[k], 1, c.H);
+      check_size(*col[k], names[k], 2, c.W);
+      check_size(*col[k], names[k], 3, 4);
+    }
+    check_dim(fwd->termination_index, "terminationIndex", 3);
+    check_size(fwd->termination_index, "terminationIndex", 0, c.B);
+    check_size(fwd->termination_index, "terminationIndex", 1, c.H);
+    check_size(fwd->termination_index, "terminationIndex", 2, c.W);
+    AdjointArgs aa;
+    std::memset(&aa, 0, sizeof(aa));
+    aa.color = strided4(fwd->color);
+    aa.adjColor = strided4(*adj_color);
+    aa.term = static_cast<const int*>(fwd->termination_index.ptr);
+    aa.tB = bstride(fwd->termination_index, 0);
+    aa.tY = bstride(fwd->termination_index, 1);
+    aa.tX = bstride(fwd->termination_index, 2);
+    check_adjoint_outputs(*adj, c.B, c.H, c.W, c.X, c.Y, c.Z, &inputs->tf, aa);
+    const bool hasVol = adj->has_volume_derivatives != 0, hasTf = adj->has_tf_derivatives != 0;
+    const bool hasRay = aa.hasStep || aa.hasCam;
+    if (!hasVol && !hasTf && !hasRay) fail(DVR_ERR_INVALID_ARGUMENT, "At least one adjoint variable must be activated!");
+    aa.compatStepOverwrite = g_compat_stepsize.load();
+    const int tf = inputs->tf_mode;
+    int tfacc = kTfAccNone;
+    if (hasTf) tfacc = (tf == kTfIdentity || c.ri.R <= kRegRows) ? kTfAccReg : kTfAccSmem;
+    const int entries = c.ri.R * tf_channels(tf);
+    const int ntab = tfacc == kTfAccSmem ? kThreads / 32 : (tfacc == kTfAccReg ? 1 : 0);
+    const size_t smem =
+        check_smem((size_t((c.ri.R * tf_row(tf) + 3) & ~3) + size_t(ntab) * entries) * sizeof(float));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    after_launch(launch_adjoint(inputs->volume_filter_mode, tf, inputs->blend_mode, hasVol, tfacc, hasRay, c.ri, aa,
+                                tile_grid(c), smem, s),
+                 "dvr_render_adjoint", s);
+  });
+}
+
+int dvr_render_forward_gradients(const DvrInputs* inputs, const DvrForwardDifferencesSettings* st,
+                                 const DvrOutputs* outputs, const DvrTensor* gradients_out, void* stream) {
+  return guarded([&] {
+    if (!inputs || !st || !outputs || !gradients_out) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    Checked c;
+    check_inputs(*inputs, c);
+    if (st->D <= 0) fail(DVR_ERR_INVALID_ARGUMENT, "number of derivatives must be positive");
+    const bool hasStep = st->d_stepsize >= 0;
+    bool hasCam = false;
+    for (int i = 0; i < 3; ++i) hasCam = hasCam || st->d_ray_start[i] >= 0 || st->d_ray_dir[i] >= 0;
+    const bool hasTf = st->has_tf_derivatives != 0;
+    if (!hasStep && !hasCam && !hasTf) fail(DVR_ERR_INVALID_ARGUMENT, "at least one derivative must be activated");
+    if (inputs->tf_mode == DVR_TF_GAUSSIAN_LOG)
+      fail(DVR_ERR_UNSUPPORTED, "forward derivatives are not supported for TFGaussianLog (deleted in the reference, renderer_tf.cuh:692-702)");
+    ForwardGradArgs ga;
+    std::memset(&ga, 0, sizeof(ga));
+    if (hasTf) {
+      if (!st->d_tf.ptr)
+        fail(DVR_ERR_INVALID_ARGUMENT, "d_tf not defined, hence hasTfDerivatives must be false but was set to true");
+      check_dim(st->d_tf, "d_tf", 3);
+      check_size(st->d_tf, "d_tf", 0, inputs->tf.size[0]);
+      check_size(st->d_tf, "d_tf", 1, inputs->tf.size[1]);
+      check_size(st->d_tf, "d_tf", 2, inputs->tf.size[2]);
+      ga.dTf = static_cast<const int*>(st->d_tf.ptr);
+      ga.dtB = bstride(st->d_tf, 0); ga.dtR = st->d_tf.stride[1]; ga.dtC = st->d_tf.stride[2];
+    }
+    const ForwardOutputs fo = check_outputs(*outputs, c);
+    check_dim(*gradients_out, "gradientsOut", 5);
+    check_size(*gradients_out, "gradientsOut", 0, c.B);
+    check_size(*gradients_out, "gradientsOut", 1, c.H);
+    check_size(*gradients_out, "gradientsOut", 2, c.W);
+    check_size(*gradients_out, "gradientsOut", 3, st->D);
+    check_size(*gradients_out, "gradientsOut", 4, 4);
+    ga.D = st->D;
+    fill_fd_settings(*st, &ga.dStep, ga.dRayStart, ga.dRayDir);
+    ga.grad = static_cast<float*>(gradients_out->ptr);
+    ga.gB = gradients_out->stride[0]; ga.gY = gradients_out->stride[1]; ga.gX = gradients_out->stride[2];
+    ga.gD = gradients_out->stride[3]; ga.gC = gradients_out->stride[4];
+    const int tf = inputs->tf_mode;
+    const size_t smem = check_smem(size_t(((c.ri.R * tf_row(tf) + 3) & ~3) + c.ri.R * tf_row(tf)) * sizeof(float));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    // ceil(D / chunk) marching passes over disjoint slot ranges
+    int d0 = 0;
+    while (d0 < st->D) {
+      const int left = st->D - d0;
+      const int chunk = left == 1 ? 1 : (left <= 6 ? 6 : 8);
+      ga.d0 = d0;
+      ga.writeColor = d0 == 0;
+      after_launch(launch_forward_gradients(inputs->volume_filter_mode, tf, inputs->blend_mode, chunk,
+                                            hasStep || hasCam, hasTf, c.ri, fo, ga, tile_grid(c), smem, s),
+                   "dvr_render_forward_gradients", s);
+      d0 += chunk;
+    }
+  });
+}
+
+int dvr_forward_variables_to_gradients(const DvrTensor* fv, const DvrTensor* gc, const DvrForwardDifferencesSettings* st,
+                                       const DvrAdjointOutputs* adj, void* stream) {
+  return guarded([&] {
+    if (!fv || !gc || !st || !adj) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    check_dim(*fv, "forwardVariables", 5);
+    const int B = int(fv->size[0]), H = int(fv->size[1]), W = int(fv->size[2]), D = int(fv->size[3]);
+    check_size(*fv, "forwardVariables", 4, 4);
+    check_dim(*gc, "gradientOutputColor", 4);
+    check_size(*gc, "gradientOutputColor", 0, B);
+    check_size(*gc, "gradientOutputColor", 1, H);
+    check_size(*gc, "gradientOutputColor", 2, W);
+    check_size(*gc, "gradientOutputColor", 3, 4);
+    if (adj->has_volume_derivatives)
+      fail(DVR_ERR_INVALID_ARGUMENT, "volume derivatives are not supported with forward variables");
+    if (B > 65535) fail(DVR_ERR_UNSUPPORTED, "batch size %d exceeds 65535", B);
+    AdjointArgs aa;
+    std::memset(&aa, 0, sizeof(aa));
+    check_adjoint_outputs(*adj, B, H, W, -1, -1, -1, nullptr, aa);
+    FwdVarsArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.W = W; a.H = H; a.B = B; a.D = D;
+    a.fv = static_cast<const float*>(fv->ptr);
+    a.fB = fv->stride[0]; a.fY = fv->stride[1]; a.fX = fv->stride[2]; a.fD = fv->stride[3]; a.fC = fv->stride[4];
+    a.gradColor = strided4(*gc);
+    fill_fd_settings(*st, &a.dStep, a.dRayStart, a.dRayDir);
+    auto need = [&](int d, bool have, const char* what) {
+      if (d >= D) fail(DVR_ERR_INVALID_ARGUMENT, "derivative slot %d of %s exceeds D=%d", d, what, D);
+      if (d >= 0 && !have) fail(DVR_ERR_INVALID_ARGUMENT, "%s derivative requested but the adjoint output is not enabled", what);
+    };
+    need(a.dStep, aa.hasStep, "stepsize");
+    for (int i = 0; i < 3; ++i) {
+      need(a.dRayStart[i], aa.hasCam, "rayStart");
+      need(a.dRayDir[i], aa.hasCam, "rayDir");
+    }
+    a.hasTf = st->has_tf_derivatives != 0;
+    if (a.hasTf) {
+      check_dim(st->d_tf, "d_tf", 3);
+      if (!adj->has_tf_derivatives) fail(DVR_ERR_INVALID_ARGUMENT, "TF derivative requested but adj_tf is not enabled");
+      check_size(adj->adj_tf, "adj_tf", 1, st->d_tf.size[1]);
+      check_size(adj->adj_tf, "adj_tf", 2, st->d_tf.size[2]);
+      a.dTf = static_cast<const int*>(st->d_tf.ptr);
+      a.dtB = bstride(st->d_tf, 0); a.dtR = st->d_tf.stride[1]; a.dtC = st->d_tf.stride[2];
+      a.R = int(st->d_tf.size[1]);
+      a.C = int(st->d_tf.size[2]);
+    }
+    a.adjStep = aa.adjStep; a.asB = aa.asB; a.asY = aa.asY; a.asX = aa.asX;
+    a.adjRayStart = aa.adjRayStart; a.rsB = aa.rsB; a.rsY = aa.rsY; a.rsX = aa.rsX; a.rsC = aa.rsC;
+    a.adjRayDir = aa.adjRayDir; a.rdB = aa.rdB; a.rdY = aa.rdY; a.rdX = aa.rdX; a.rdC = aa.rdC;
+    a.adjTf = aa.adjTf; a.atB = aa.atB; a.atR = aa.atR; a.atC = aa.atC;
+    check_smem(size_t(a.R) * a.C * sizeof(float));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    after_launch(launch_fwdvars_to_gradients(a, s), "dvr_forward_variables_to_gradients", s);
+  });
+}
+
+int dvr_count_cell_visits(const DvrInputs* inputs, const DvrTensor* termination_index, uint64_t* counts,
+                          void* stream) {
+  return guarded([&] {
+    if (!inputs || !termination_index || !counts) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    Checked c;
+    check_inputs(*inputs, c);
+    check_dim(*termination_index, "terminationIndex", 3);
+    check_size(*termination_index, "terminationIndex", 0, c.B);
+    check_size(*termination_index, "terminationIndex", 1, c.H);
+    check_size(*termination_index, "terminationIndex", 2, c.W);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    after_launch(launch_count_cells(c.ri, static_cast<const int*>(termination_index->ptr),
+                                    termination_index->stride[0], termination_index->stride[1],
+                                    termination_index->stride[2],
+                                    reinterpret_cast<unsigned long long*>(counts), tile_grid(c), s),
+                 "dvr_count_cell_visits", s);
+  });
+}
+
+int dvr_has_variant(int32_t filter, int32_t camera, int32_t tf, int32_t blend) {
+  const bool f = filter == DVR_FILTER_NEAREST || filter == DVR_FILTER_TRILINEAR;
+  const bool c = camera >= 0 && camera <= 2;
+  const bool t = tf == DVR_TF_IDENTITY || tf == DVR_TF_TEXTURE || tf == DVR_TF_LINEAR || tf == DVR_TF_GAUSSIAN ||
+                 tf == DVR_TF_GAUSSIAN_LOG;
+  const bool b = blend == DVR_BLEND_BEER_LAMBERT || blend == DVR_BLEND_ALPHA;
+  return f && c && t && b;
+}
+
+int dvr_set_option(const char* name, int32_t value) {
+  if (!name) return DVR_ERR_INVALID_ARGUMENT;
+  if (!std::strcmp(name, "sync_mode")) { g_sync_mode = value; return DVR_OK; }
+  if (!std::strcmp(name, "compat_stepsize_overwrite")) { g_compat_stepsize = value; return DVR_OK; }
+  if (!std::strcmp(name, "volume_layout")) { g_volume_layout = value; return DVR_OK; }
+  g_error = std::string("unknown option '") + name + "'";
+  return DVR_ERR_INVALID_ARGUMENT;
+}
+
+int dvr_get_option(const char* name, int32_t* value) {
+  if (!name || !value) return DVR_ERR_INVALID_ARGUMENT;
+  if (!std::strcmp(name, "sync_mode")) { *value = g_sync_mode; return DVR_OK; }
+  if (!std::strcmp(name, "compat_stepsize_overwrite")) { *value = g_compat_stepsize; return DVR_OK; }
+  if (!std::strcmp(name, "volume_layout")) { *value = g_volume_layout; return DVR_OK; }
+  g_error = std::string("unknown option '") + name + "'";
+  return DVR_ERR_INVALID_ARGUMENT;
+}
+
+int64_t dvr_launch_count(void) { return g_launches.load(); }
+const char* dvr_last_error(void) { return g_error.c_str(); }
+int32_t dvr_abi_version(void) { return DVR_ABI_VERSION; }
+
+}  // extern "C"

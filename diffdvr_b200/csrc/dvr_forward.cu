@@ -1,0 +1,31 @@
+// Instances of the plain forward kernel: {Nearest, Trilinear} x {Identity, Texture, Linear,
+// Gaussian, GaussianLog} x {BeerLambert, Alpha}. The camera mode is a run-time switch outside
+// the marching loop, so the reference's 3 camera instantiations collapse into one.
+#include "dvr_kernels.cuh"
+#include "dvr_launch.h"
+
+namespace dvr {
+
+template <int F, int B>
+static cudaError_t by_tf(int tf, const RayInputs& in, const ForwardOutputs& out, dim3 grid, size_t smem,
+                         cudaStream_t s) {
+  switch (tf) {
+    case kTfIdentity: return launch_kernel(k_forward<F, kTfIdentity, B>, grid, kThreads, smem, s, in, out);
+    case kTfTexture: return launch_kernel(k_forward<F, kTfTexture, B>, grid, kThreads, smem, s, in, out);
+    case kTfLinear: return launch_kernel(k_forward<F, kTfLinear, B>, grid, kThreads, smem, s, in, out);
+    case kTfGaussian: return launch_kernel(k_forward<F, kTfGaussian, B>, grid, kThreads, smem, s, in, out);
+    case kTfGaussianLog: return launch_kernel(k_forward<F, kTfGaussianLog, B>, grid, kThreads, smem, s, in, out);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+cudaError_t launch_forward(int filter, int tf, int blend, const RayInputs& in, const ForwardOutputs& out,
+                           dim3 grid, size_t smem, cudaStream_t s) {
+  if (filter == kFilterNearest && blend == kBlendBeer) return by_tf<kFilterNearest, kBlendBeer>(tf, in, out, grid, smem, s);
+  if (filter == kFilterNearest && blend == kBlendAlpha) return by_tf<kFilterNearest, kBlendAlpha>(tf, in, out, grid, smem, s);
+  if (filter == kFilterTrilinear && blend == kBlendBeer) return by_tf<kFilterTrilinear, kBlendBeer>(tf, in, out, grid, smem, s);
+  if (filter == kFilterTrilinear && blend == kBlendAlpha) return by_tf<kFilterTrilinear, kBlendAlpha>(tf, in, out, grid, smem, s);
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace dvr

@@ -1,0 +1,216 @@
+// sm_100a kernels: forward-mode differentiation (DvrKernelForwardGradientsImpl,
+// renderer/renderer_kernels.cuh:161-255) and the forward-variables -> gradients contraction
+// (ForwardVariablesToGradientsKernelImpl, :504-561).
+//
+// The reference instantiates cudAD::fvar<T,D> for the full D at run time through NVRTC; here
+// the dual number carries a compile-time CHUNK of N tangent slots and the host runs
+// ceil(D/N) passes, each re-marching the ray for the slots [d0, d0+N) and writing a disjoint
+// slice of the B*H*W*D*4 Jacobian (the value part is identical in every pass).
+#pragma once
+#include "dvr_device.cuh"
+
+namespace dvr {
+
+template <int N>
+struct Du {
+  float v;
+  float d[N];
+};
+
+template <int N> DVR_DEV Du<N> du_const(float v) {
+  Du<N> r;
+  r.v = v;
+#pragma unroll
+  for (int i = 0; i < N; ++i) r.d[i] = 0.f;
+  return r;
+}
+// fvar::input: unit tangent in slot (idx - d0) if that slot belongs to this pass
+template <int N> DVR_DEV Du<N> du_input(float v, int idx, int d0) {
+  Du<N> r;
+  r.v = v;
+  const int s = idx - d0;
+#pragma unroll
+  for (int i = 0; i < N; ++i) r.d[i] = (idx >= 0 && i == s) ? 1.f : 0.f;
+  return r;
+}
+template <int N> DVR_DEV float val(const Du<N>& a) { return a.v; }
+DVR_DEV float val(float a) { return a; }
+
+#define DVR_DU_LOOP _Pragma("unroll") for (int i = 0; i < N; ++i)
+template <int N> DVR_DEV Du<N> operator+(const Du<N>& a, const Du<N>& b) { Du<N> r; r.v = a.v + b.v; DVR_DU_LOOP r.d[i] = a.d[i] + b.d[i]; return r; }
+template <int N> DVR_DEV Du<N> operator+(const Du<N>& a, float b) { Du<N> r = a; r.v = a.v + b; return r; }
+template <int N> DVR_DEV Du<N> operator+(float a, const Du<N>& b) { Du<N> r = b; r.v = a + b.v; return r; }
+template <int N> DVR_DEV Du<N> operator-(const Du<N>& a, const Du<N>& b) { Du<N> r; r.v = a.v - b.v; DVR_DU_LOOP r.d[i] = a.d[i] - b.d[i]; return r; }
+template <int N> DVR_DEV Du<N> operator-(const Du<N>& a, float b) { Du<N> r = a; r.v = a.v - b; return r; }
+template <int N> DVR_DEV Du<N> operator-(float a, const Du<N>& b) { Du<N> r; r.v = a - b.v; DVR_DU_LOOP r.d[i] = -b.d[i]; return r; }
+template <int N> DVR_DEV Du<N> operator-(const Du<N>& a) { Du<N> r; r.v = -a.v; DVR_DU_LOOP r.d[i] = -a.d[i]; return r; }
+template <int N> DVR_DEV Du<N> operator*(const Du<N>& a, const Du<N>& b) { Du<N> r; r.v = a.v * b.v; DVR_DU_LOOP r.d[i] = fmaf(a.d[i], b.v, a.v * b.d[i]); return r; }
+template <int N> DVR_DEV Du<N> operator*(const Du<N>& a, float b) { Du<N> r; r.v = a.v * b; DVR_DU_LOOP r.d[i] = a.d[i] * b; return r; }
+template <int N> DVR_DEV Du<N> operator*(float a, const Du<N>& b) { return b * a; }
+template <int N> DVR_DEV Du<N> operator/(const Du<N>& a, const Du<N>& b) {
+  Du<N> r;
+  const float inv = 1.0f / b.v;
+  r.v = a.v * inv;
+  DVR_DU_LOOP r.d[i] = (a.d[i] - r.v * b.d[i]) * inv;  // (a'b - ab')/b^2
+  return r;
+}
+template <int N> DVR_DEV Du<N> operator/(const Du<N>& a, float b) { return a * (1.0f / b); }
+template <int N> DVR_DEV Du<N> du_exp(const Du<N>& a) { Du<N> r; r.v = expf(a.v); DVR_DU_LOOP r.d[i] = a.d[i] * r.v; return r; }
+DVR_DEV float du_exp(float a) { return expf(a); }
+// selection rules of the restated cudAD (oracle/cudad_restated/forward.h): a<b ? a : b
+template <int N> DVR_DEV Du<N> du_min(const Du<N>& a, const Du<N>& b) { return a.v < b.v ? a : b; }
+template <int N> DVR_DEV Du<N> du_max(const Du<N>& a, const Du<N>& b) { return a.v > b.v ? a : b; }
+template <int N> DVR_DEV Du<N> du_clamp(const Du<N>& x, const Du<N>& lo, const Du<N>& hi) { return du_max(lo, du_min(x, hi)); }
+template <int N> DVR_DEV Du<N> du_lerp(const Du<N>& a, const Du<N>& b, const Du<N>& t) { return a + t * (b - a); }
+template <int N> DVR_DEV Du<N> du_lerp(float a, float b, const Du<N>& t) { return a + t * (b - a); }
+template <int N> DVR_DEV Du<N> du_lerp(const Du<N>& a, const Du<N>& b, float t) { return a + (b - a) * t; }
+template <int N> DVR_DEV Du<N> du_lerp(float a, float b, float t) { return du_const<N>(lerpf(a, b, t)); }
+#undef DVR_DU_LOOP
+
+template <int N> struct Du4 { Du<N> x, y, z, w; };
+
+// TF evaluation in dual numbers (renderer_tf.cuh:121-154, 255-288, 436-485, 521-560).
+// DENS is float (no positional tangents) or Du<N>. s_dtf mirrors s_tf's layout with the
+// tangent slot of every TF entry (or is unused when !HAS_TF).
+template <int TF, int N, bool HAS_TF, typename DENS>
+DVR_DEV Du4<N> tf_eval_dual(const float* s_tf, const int* s_dtf, int R, const DENS& density, int d0) {
+  constexpr int ROW = TfLayout<TF>::kRow;
+  auto seed = [&](int r, int c) {
+    if constexpr (HAS_TF) return du_input<N>(s_tf[r * ROW + c], s_dtf[r * ROW + c], d0);
+    else return du_const<N>(s_tf[r * ROW + c]);
+  };
+  auto dens = [&]() {
+    if constexpr (sizeof(DENS) == sizeof(float)) return du_const<N>(density);
+    else return density;
+  };
+  if constexpr (TF == kTfIdentity) {
+    const Du<N> dc = du_clamp(dens(), du_const<N>(0.f), du_const<N>(1.f));
+    const Du<N> sa = seed(0, 0), sc = seed(0, 1);
+    const Du<N> col = dc * sc;
+    return {col, col, col, dc * sa};
+  } else if constexpr (TF == kTfTexture) {
+    const Du<N> d = dens() * float(R) - 0.5f;
+    const int di = int(floorf(d.v));
+    const Du<N> df = d - float(di);
+    const int i0 = min(max(di, 0), R - 1), i1 = min(max(di + 1, 0), R - 1);
+    return {du_lerp(seed(i0, 0), seed(i1, 0), df), du_lerp(seed(i0, 1), seed(i1, 1), df),
+            du_lerp(seed(i0, 2), seed(i1, 2), df), du_lerp(seed(i0, 3), seed(i1, 3), df)};
+  } else if constexpr (TF == kTfLinear) {
+    const Du<N> dd = dens();
+    const int i = linear_interval(s_tf, R, dd.v);
+    const Du<N> p0 = seed(i, 4), p1 = seed(i + 1, 4);
+    const Du<N> d2 = du_clamp(dd, p0, p1);
+    const Du<N> frac = (d2 - p0) / (p1 - p0);
+    return {du_lerp(seed(i, 0), seed(i + 1, 0), frac), du_lerp(seed(i, 1), seed(i + 1, 1), frac),
+            du_lerp(seed(i, 2), seed(i + 1, 2), frac), du_lerp(seed(i, 3), seed(i + 1, 3), frac)};
+  } else {  // kTfGaussian
+    const Du<N> dd = dens();
+    Du4<N> c = {du_const<N>(0.f), du_const<N>(0.f), du_const<N>(0.f), du_const<N>(0.f)};
+    for (int i = 0; i < R; ++i) {
+      const Du<N> mu = seed(i, 4), sigma = seed(i, 5);
+      const Du<N> diff = dd - mu;
+      const Du<N> ni = du_exp(-(diff * diff) / (2.0f * sigma * sigma));
+      c.x = c.x + seed(i, 0) * ni;
+      c.y = c.y + seed(i, 1) * ni;
+      c.z = c.z + seed(i, 2) * ni;
+      c.w = c.w + seed(i, 3) * ni;
+    }
+    return c;
+  }
+}
+
+// HAS_POS: stepsize and/or ray tangents are traced (position, t and stepsize are dual)
+template <int FILTER, int TF, int BLEND, int N, bool HAS_POS, bool HAS_TF>
+__global__ void __launch_bounds__(kThreads) k_forward_gradients(const RayInputs in, const ForwardOutputs out,
+                                                                const ForwardGradArgs ga) {
+  extern __shared__ __align__(16) float smem[];
+  constexpr int ROW = TfLayout<TF>::kRow;
+  const int b = blockIdx.z;
+  float* s_tf = smem;
+  int* s_dtf = reinterpret_cast<int*>(smem + ((in.R * ROW + 3) & ~3));
+  stage_tf<TF>(in, b, s_tf);
+  if constexpr (HAS_TF) {
+    const int* src = ga.dTf + b * ga.dtB;
+    for (int i = threadIdx.x; i < in.R * ROW; i += blockDim.x) {
+      const int r = i / ROW, c = i - r * ROW;
+      s_dtf[i] = c < in.C ? __ldg(src + r * ga.dtR + c * ga.dtC) : -1;
+    }
+  }
+  __syncthreads();
+  int x, y;
+  thread_pixel(x, y);
+  if (x >= in.W || y >= in.H) return;
+
+  const Ray ray = make_ray(in, x, y, b);  // box intersection on VALUES only (:201-208)
+  const int d0 = ga.d0;
+  // volume-space affine ray with tangents: ps = (start-boxMin)/voxel, pd = dir/voxel
+  Du<N> psx, psy, psz, pdx, pdy, pdz, step;
+  if constexpr (HAS_POS) {
+    psx = du_input<N>(ray.ps.x, ga.dRayStart[0], d0) ; psy = du_input<N>(ray.ps.y, ga.dRayStart[1], d0); psz = du_input<N>(ray.ps.z, ga.dRayStart[2], d0);
+    pdx = du_input<N>(ray.pd.x, ga.dRayDir[0], d0); pdy = du_input<N>(ray.pd.y, ga.dRayDir[1], d0); pdz = du_input<N>(ray.pd.z, ga.dRayDir[2], d0);
+#pragma unroll
+    for (int i = 0; i < N; ++i) {  // chain rule of the division by voxelSize
+      psx.d[i] *= ray.invVoxel.x; psy.d[i] *= ray.invVoxel.y; psz.d[i] *= ray.invVoxel.z;
+      pdx.d[i] *= ray.invVoxel.x; pdy.d[i] *= ray.invVoxel.y; pdz.d[i] *= ray.invVoxel.z;
+    }
+    step = du_input<N>(ray.step, ga.dStep, d0);
+  }
+  Sampler<FILTER, false> smp;
+  smp.init(in, b, nullptr, 0);
+  Du4<N> acc = {du_const<N>(0.f), du_const<N>(0.f), du_const<N>(0.f), du_const<N>(0.f)};
+  int i = 0;
+  float fi = 0.f;
+  for (;; ++i, fi += 1.0f) {
+    const float t = sample_t(ray, fi);
+    if (t > ray.tmax) break;
+    if (acc.w.v > in.earlyOut) break;
+    const float px = fmaf(t, ray.pd.x, ray.ps.x), py = fmaf(t, ray.pd.y, ray.ps.y), pz = fmaf(t, ray.pd.z, ray.ps.z);
+    const float density = smp.fetch(in, nullptr, px, py, pz);
+    Du4<N> cur;
+    Du<N> alpha;
+    if constexpr (HAS_POS) {
+      Du<N> dd;
+      if constexpr (FILTER == kFilterNearest) {
+        dd = du_const<N>(density);  // no positional tangent (interpolation.cuh:52-65)
+      } else {
+        // t = tmin + i*step: dt/dstep = i; positions keep the value computed above
+        Du<N> td = step * fi;
+        td.v = t;
+        Du<N> fxd = psx + td * pdx, fyd = psy + td * pdy, fzd = psz + td * pdz;
+        fxd.v = smp.fx; fyd.v = smp.fy; fzd.v = smp.fz;  // fractional parts share the tangents
+        const float* d = smp.d;
+        dd = du_lerp(du_lerp(du_lerp(d[0], d[4], fxd), du_lerp(d[2], d[6], fxd), fyd),
+                     du_lerp(du_lerp(d[1], d[5], fxd), du_lerp(d[3], d[7], fxd), fyd), fzd);
+      }
+      cur = tf_eval_dual<TF, N, HAS_TF>(s_tf, s_dtf, in.R, dd, d0);
+      if constexpr (BLEND == kBlendBeer) alpha = 1.0f - du_exp(-(cur.w * step));
+      else alpha = du_min(du_const<N>(1.f), cur.w * step);
+    } else {
+      cur = tf_eval_dual<TF, N, HAS_TF>(s_tf, s_dtf, in.R, density, d0);
+      if constexpr (BLEND == kBlendBeer) alpha = 1.0f - du_exp(-(cur.w * ray.step));
+      else alpha = du_min(du_const<N>(1.f), cur.w * ray.step);
+    }
+    // Blending::blend generic (renderer_blending.cuh:40-51, 105-116)
+    const Du<N> om = 1.0f - acc.w;
+    acc.x = acc.x + om * cur.x * alpha;
+    acc.y = acc.y + om * cur.y * alpha;
+    acc.z = acc.z + om * cur.z * alpha;
+    acc.w = acc.w + om * alpha;
+  }
+  if (ga.writeColor) {
+    float* c = out.color + b * out.cB + y * out.cY + x * out.cX;
+    c[0] = acc.x.v; c[out.cC] = acc.y.v; c[2 * out.cC] = acc.z.v; c[3 * out.cC] = acc.w.v;
+    out.term[b * out.tB + y * out.tY + x * out.tX] = i;
+  }
+  float* g = ga.grad + b * ga.gB + y * ga.gY + x * ga.gX;
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    const int d = d0 + k;
+    if (d < ga.D) {
+      float* gd = g + d * ga.gD;
+      gd[0] = acc.x.d[k]; gd[ga.gC] = acc.y.d[k]; gd[2 * ga.gC] = acc.z.d[k]; gd[3 * ga.gC] = acc.w.d[k];
+    }
+  }
+}
+
+}  // namespace dvr

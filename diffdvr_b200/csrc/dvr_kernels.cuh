@@ -1,0 +1,347 @@
+// sm_100a kernels: plain forward render and adjoint pass.
+// One thread marches one ray; a warp owns an 8x4 pixel tile so that its 32 rays stay in
+// neighbouring cells (coherent L1 sectors, coherent trip counts); a CTA owns 16x8 pixels of one
+// view (blockIdx.z = batch entry), stages that view's transfer function in shared memory once
+// and, in the adjoint, owns a shared-memory accumulator for the TF gradient that is flushed to
+// global memory once per CTA.
+#pragma once
+#include "dvr_device.cuh"
+
+namespace dvr {
+
+// ===============================================================================================
+// forward: DvrKernelForwardImpl (renderer/renderer_kernels.cuh:22-90)
+// ===============================================================================================
+template <int FILTER, int TF, int BLEND>
+__global__ void __launch_bounds__(kThreads) k_forward(const RayInputs in, const ForwardOutputs out) {
+  extern __shared__ __align__(16) float smem[];
+  const int b = blockIdx.z;
+  stage_tf<TF>(in, b, smem);
+  __syncthreads();
+  int x, y;
+  thread_pixel(x, y);
+  if (x >= in.W || y >= in.H) return;
+
+  const Ray ray = make_ray(in, x, y, b);
+  Sampler<FILTER, false> smp;
+  smp.init(in, b, nullptr, 0);
+  f4 acc = {0.f, 0.f, 0.f, 0.f};
+  int i = 0;
+  float fi = 0.f;
+  for (;; ++i, fi += 1.0f) {
+    const float t = sample_t(ray, fi);
+    if (t > ray.tmax) break;
+    if (acc.w > in.earlyOut) break;
+    const float density = smp.fetch(in, nullptr, fmaf(t, ray.pd.x, ray.ps.x), fmaf(t, ray.pd.y, ray.ps.y),
+                                    fmaf(t, ray.pd.z, ray.ps.z));
+    const f4 cur = tf_eval<TF>(smem, in.R, density);
+    acc = blend_over(acc, cur, blend_alpha<BLEND>(cur.w, ray.step));
+  }
+  float* c = out.color + b * out.cB + y * out.cY + x * out.cX;
+  if (out.colorVec4) {
+    *reinterpret_cast<float4*>(c) = make_float4(acc.x, acc.y, acc.z, acc.w);
+  } else {
+    c[0] = acc.x; c[out.cC] = acc.y; c[2 * out.cC] = acc.z; c[3 * out.cC] = acc.w;
+  }
+  out.term[b * out.tB + y * out.tY + x * out.tX] = i;
+}
+
+// ===============================================================================================
+// adjoint: DvrKernelAdjointImpl (renderer/renderer_kernels.cuh:315-444)
+// ===============================================================================================
+// TF-gradient accumulation strategies (replace both the reference's immediate mode -- 8..12
+// global atomics per SAMPLE, renderer_tf.cuh:208-216 -- and its delayed mode -- R*C floats of
+// shared memory per THREAD, renderer_cuda.cpp:273-295):
+//   kTfAccReg : R <= kRegRows: per-thread register accumulators, one warp-shuffle reduction and
+//               one shared-memory atomic per table entry per WARP at the end of the ray
+//   kTfAccSmem: larger tables: per-warp private table in shared memory; Texture/Linear keep the
+//               two rows they are currently touching in registers and flush on a row change
+// Either way global memory sees R*C atomics per CTA.
+enum : int { kTfAccNone = 0, kTfAccReg = 1, kTfAccSmem = 2 };
+constexpr int kRegRows = 6;
+
+template <int TF> struct TfChannels { static constexpr int v = 6; };
+template <> struct TfChannels<kTfIdentity> { static constexpr int v = 2; };
+template <> struct TfChannels<kTfTexture> { static constexpr int v = 4; };
+template <> struct TfChannels<kTfLinear> { static constexpr int v = 5; };
+
+template <int TF, int TFACC>
+struct TfGrad {
+  static constexpr int CH = TfChannels<TF>::v;
+  static constexpr int NREG = TFACC == kTfAccReg ? kRegRows * CH : 1;
+  float g[NREG];     // kTfAccReg: whole table; indexing is fully unrolled (stays in registers)
+  float row[2][CH];  // kTfAccSmem (Texture/Linear): cached rows base, base+1
+  int base;
+  float* table;      // kTfAccSmem: this warp's table
+
+  DVR_DEV void init(float* warpTable) {
+#pragma unroll
+    for (int i = 0; i < NREG; ++i) g[i] = 0.f;
+#pragma unroll
+    for (int c = 0; c < CH; ++c) row[0][c] = row[1][c] = 0.f;
+    base = -2;  // never aliases a valid row or row-1
+    table = warpTable;
+  }
+  DVR_DEV void flush_rows() {
+    if (base >= 0) {
+#pragma unroll
+      for (int c = 0; c < CH; ++c) {
+        if (row[0][c] != 0.f) atomicAdd(table + base * CH + c, row[0][c]);
+        if (row[1][c] != 0.f) atomicAdd(table + (base + 1) * CH + c, row[1][c]);
+        row[0][c] = row[1][c] = 0.f;
+      }
+    }
+  }
+  // contribution v[0..CH) to row r (two-row modes call this with r = i and r = i or i+1)
+  DVR_DEV void add_row(int r, const float* v) {
+    if constexpr (TFACC == kTfAccReg) {
+#pragma unroll
+      for (int rr = 0; rr < kRegRows; ++rr)
+        if (rr == r) {
+#pragma unroll
+          for (int c = 0; c < CH; ++c) g[rr * CH + c] += v[c];
+        }
+    } else if constexpr (TF == kTfTexture || TF == kTfLinear) {
+      if (r != base && r != base + 1) {  // only the first of the two calls can miss
+        flush_rows();
+        base = r;
+      }
+      if (r == base) {
+#pragma unroll
+        for (int c = 0; c < CH; ++c) row[0][c] += v[c];
+      } else {
+#pragma unroll
+        for (int c = 0; c < CH; ++c) row[1][c] += v[c];
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < CH; ++c) atomicAdd(table + r * CH + c, v[c]);
+    }
+  }
+};
+
+// adjoint of tf_eval; returns adj_density and adds the parameter adjoints to `acc`
+template <int TF, int TFACC>
+DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC, TfGrad<TF, TFACC>& acc) {
+  constexpr bool HAS_TF = TFACC != kTfAccNone;
+  if constexpr (TF == kTfIdentity) {  // renderer_tf.cuh:75-104
+    const float dc = fmaxf(0.f, fminf(density, 1.f));
+    const float sa = s_tf[0], sc = s_tf[1];
+    const float adjDc = (adjC.x * sc + adjC.y * sc + adjC.z * sc) + adjC.w * sa;
+    if constexpr (HAS_TF) {
+      acc.g[0] += adjC.w * dc;                               // d/d scaleAbsorption
+      acc.g[1] += adjC.x * dc + adjC.y * dc + adjC.z * dc;   // d/d scaleColor
+    }
+    return (density > 0.f && density < 1.f) ? adjDc : 0.f;
+  } else if constexpr (TF == kTfTexture) {  // :173-220
+    int i0, i1;
+    float df;
+    texture_coords(density, R, i0, i1, df);
+    const f4 v0 = lds4(s_tf + 4 * i0), v1 = lds4(s_tf + 4 * i1);
+    const float adjDf = dot4(adjC, f4{v1.x - v0.x, v1.y - v0.y, v1.z - v0.z, v1.w - v0.w});
+    if constexpr (HAS_TF) {
+      const float w0 = 1.f - df;
+      const float a0[4] = {adjC.x * w0, adjC.y * w0, adjC.z * w0, adjC.w * w0};
+      const float a1[4] = {adjC.x * df, adjC.y * df, adjC.z * df, adjC.w * df};
+      acc.add_row(i0, a0);
+      acc.add_row(i1, a1);
+    }
+    return adjDf * float(R);
+  } else if constexpr (TF == kTfLinear) {  // :315-400
+    const int i = linear_interval(s_tf, R, density);
+    const f4 v0 = lds4(s_tf + 8 * i), v1 = lds4(s_tf + 8 * (i + 1));
+    const float p0 = s_tf[8 * i + 4], p1 = s_tf[8 * (i + 1) + 4];
+    const float d2 = fmaxf(p0, fminf(density, p1));
+    const float frac = (d2 - p0) / (p1 - p0);
+    const float adjFrac = dot4(adjC, f4{v1.x - v0.x, v1.y - v0.y, v1.z - v0.z, v1.w - v0.w});
+    if constexpr (HAS_TF) {
+      const float denom = (p1 - p0) * (p1 - p0);
+      const float w0 = 1.f - frac;
+      const float a0[5] = {adjC.x * w0, adjC.y * w0, adjC.z * w0, adjC.w * w0, adjFrac * (d2 - p1) / denom};
+      const float a1[5] = {adjC.x * frac, adjC.y * frac, adjC.z * frac, adjC.w * frac, adjFrac * (p0 - d2) / denom};
+      acc.add_row(i, a0);
+      acc.add_row(i + 1, a1);
+    }
+    return adjFrac / (p1 - p0);  // passes through the clamp unconditionally ("#if 1", :350-352)
+  } else if constexpr (TF == kTfGaussian) {  // :562-614
+    float adjDensity = 0.f;
+    auto body = [&](int i, float* g) {
+      const f4 ci = lds4(s_tf + 8 * i);
+      const float mu = s_tf[8 * i + 4], sigma = s_tf[8 * i + 5];
+      const float ni = expf(gauss_arg(density, mu, sigma));
+      const float f1 = (mu - density) / (sigma * sigma) * ni;
+      const float dc = dot4(adjC, ci);
+      adjDensity = fmaf(dc, f1, adjDensity);
+      if constexpr (HAS_TF) {
+        const float f2 = f1 * (mu - density) / sigma;
+        g[0] = adjC.x * ni; g[1] = adjC.y * ni; g[2] = adjC.z * ni; g[3] = adjC.w * ni;
+        g[4] = -dc * f1;
+        g[5] = dc * f2;
+      }
+    };
+    if constexpr (TFACC == kTfAccReg) {
+#pragma unroll
+      for (int i = 0; i < kRegRows; ++i)
+        if (i < R) {
+          float g[6];
+          body(i, g);
+#pragma unroll
+          for (int c = 0; c < 6; ++c) acc.g[i * 6 + c] += g[c];
+        }
+    } else {
+      for (int i = 0; i < R; ++i) {
+        float g[6];
+        body(i, g);
+        if constexpr (HAS_TF) acc.add_row(i, g);
+      }
+    }
+    return adjDensity;
+  } else {  // kTfGaussianLog, :705-780
+    float adjDensity = 0.f;
+    auto tval = [&](int i) {
+      const f4 ci = lds4(s_tf + 8 * i);
+      const float ln = gauss_arg(density, s_tf[8 * i + 4], s_tf[8 * i + 5]);
+      return f4{logf(ci.x) + ln, logf(ci.y) + ln, logf(ci.z) + ln, logf(ci.w) + ln};
+    };
+    auto body = [&](int i, float* g) {
+      const f4 ci = lds4(s_tf + 8 * i);
+      const float mu = s_tf[8 * i + 4], sigma = s_tf[8 * i + 5];
+      const f4 ti = tval(i);
+      f4 den = {1.f, 1.f, 1.f, 1.f};
+      for (int j = 0; j < R; ++j)
+        if (j != i) {
+          const f4 tj = tval(j);
+          den.x += expf(tj.x - ti.x); den.y += expf(tj.y - ti.y); den.z += expf(tj.z - ti.z); den.w += expf(tj.w - ti.w);
+        }
+      const f4 adjTi = {adjC.x / den.x, adjC.y / den.y, adjC.z / den.z, adjC.w / den.w};
+      const float f1 = (mu - density) / (sigma * sigma);
+      const float adjXmu = adjTi.x * f1 + adjTi.y * f1 + adjTi.z * f1 + adjTi.w * f1;
+      adjDensity += adjXmu;
+      if constexpr (HAS_TF) {
+        const float f2 = f1 * (mu - density) / sigma;
+        g[0] = adjTi.x / ci.x; g[1] = adjTi.y / ci.y; g[2] = adjTi.z / ci.z; g[3] = adjTi.w / ci.w;
+        g[4] = -adjXmu;
+        g[5] = adjTi.x * f2 + adjTi.y * f2 + adjTi.z * f2 + adjTi.w * f2;
+      }
+    };
+    if constexpr (TFACC == kTfAccReg) {
+#pragma unroll
+      for (int i = 0; i < kRegRows; ++i)
+        if (i < R) {
+          float g[6];
+          body(i, g);
+#pragma unroll
+          for (int c = 0; c < 6; ++c) acc.g[i * 6 + c] += g[c];
+        }
+    } else {
+      for (int i = 0; i < R; ++i) {
+        float g[6];
+        body(i, g);
+        if constexpr (HAS_TF) acc.add_row(i, g);
+      }
+    }
+    return adjDensity;
+  }
+}
+
+template <int FILTER, int TF, int BLEND, bool HAS_VOL, int TFACC, bool HAS_RAY>
+__global__ void __launch_bounds__(kThreads) k_adjoint(const RayInputs in, const AdjointArgs aa) {
+  extern __shared__ __align__(16) float smem[];
+  constexpr int ROW = TfLayout<TF>::kRow;
+  constexpr int CH = TfChannels<TF>::v;
+  const int b = blockIdx.z;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* s_tf = smem;
+  float* s_acc = smem + ((in.R * ROW + 3) & ~3);  // TF-gradient tables
+  const int entries = in.R * CH;
+  constexpr int NTAB = TFACC == kTfAccSmem ? kThreads / 32 : 1;
+  stage_tf<TF>(in, b, s_tf);
+  if constexpr (TFACC != kTfAccNone)
+    for (int i = threadIdx.x; i < entries * NTAB; i += blockDim.x) s_acc[i] = 0.f;
+  __syncthreads();
+
+  int x, y;
+  thread_pixel(x, y);
+  const bool active = x < in.W && y < in.H;
+  TfGrad<TF, TFACC> tfg;
+  tfg.init(TFACC == kTfAccSmem ? s_acc + warp * entries : s_acc);
+
+  if (active) {
+    const Ray ray = make_ray(in, x, y, b);
+    const float* cp = aa.color.p + b * aa.color.b + y * aa.color.y + x * aa.color.x;
+    const float* ap = aa.adjColor.p + b * aa.adjColor.b + y * aa.adjColor.y + x * aa.adjColor.x;
+    f4 acc = {__ldg(cp), __ldg(cp + aa.color.c), __ldg(cp + 2 * aa.color.c), __ldg(cp + 3 * aa.color.c)};
+    f4 adjAcc = {__ldg(ap), __ldg(ap + aa.adjColor.c), __ldg(ap + 2 * aa.adjColor.c), __ldg(ap + 3 * aa.adjColor.c)};
+    const int n = __ldg(aa.term + b * aa.tB + y * aa.tY + x * aa.tX);
+    float adjStep = 0.f;
+    f3 adjStart = {0.f, 0.f, 0.f}, adjDir = {0.f, 0.f, 0.f};
+    Sampler<FILTER, HAS_VOL> smp;
+    smp.init(in, b, aa.adjVolume, aa.avB);
+    // terminationIndex-1 was the last sample that contributed (renderer_kernels.cuh:374-376)
+    float fi = float(n - 1);
+    for (int i = n - 1; i >= 0; --i, fi -= 1.0f) {
+      const float t = sample_t(ray, fi);
+      const float density = smp.fetch(in, &aa, fmaf(t, ray.pd.x, ray.ps.x), fmaf(t, ray.pd.y, ray.ps.y),
+                                      fmaf(t, ray.pd.z, ray.ps.z));
+      const f4 cur = tf_eval<TF>(s_tf, in.R, density);
+      f4 adjCur;
+      float adjStepBlend;
+      blend_adjoint<BLEND>(acc, adjAcc, cur, ray.step, adjCur, adjStepBlend);
+      const float adjDensity = tf_adjoint<TF, TFACC>(s_tf, in.R, density, adjCur, tfg);
+      const f3 g = smp.template adjoint<HAS_RAY>(adjDensity);
+      if constexpr (HAS_RAY) {
+        // the reference overwrites its accumulator with the blend term (see compat flag)
+        adjStep = aa.compatStepOverwrite ? adjStepBlend : adjStep + adjStepBlend;
+        const f3 w = {g.x * ray.invVoxel.x, g.y * ray.invVoxel.y, g.z * ray.invVoxel.z};
+        adjStart.x += w.x; adjStart.y += w.y; adjStart.z += w.z;
+        adjDir.x = fmaf(w.x, t, adjDir.x); adjDir.y = fmaf(w.y, t, adjDir.y); adjDir.z = fmaf(w.z, t, adjDir.z);
+        const float adjT = w.x * ray.dir.x + w.y * ray.dir.y + w.z * ray.dir.z;
+        adjStep = fmaf(adjT, fi, adjStep);
+      }
+    }
+    smp.flush();
+    if constexpr (HAS_RAY) {
+      if (aa.hasStep) {
+        float* p = aa.adjStep + b * aa.asB + y * aa.asY + x * aa.asX;
+        if (aa.stepAtomic) atomicAdd(p, adjStep);
+        else *p = adjStep;
+      }
+      if (aa.hasCam) {
+        float* ps = aa.adjRayStart + b * aa.rsB + y * aa.rsY + x * aa.rsX;
+        float* pd = aa.adjRayDir + b * aa.rdB + y * aa.rdY + x * aa.rdX;
+        if (aa.camAtomic) {
+          atomicAdd(ps, adjStart.x); atomicAdd(ps + aa.rsC, adjStart.y); atomicAdd(ps + 2 * aa.rsC, adjStart.z);
+          atomicAdd(pd, adjDir.x); atomicAdd(pd + aa.rdC, adjDir.y); atomicAdd(pd + 2 * aa.rdC, adjDir.z);
+        } else {
+          ps[0] = adjStart.x; ps[aa.rsC] = adjStart.y; ps[2 * aa.rsC] = adjStart.z;
+          pd[0] = adjDir.x; pd[aa.rdC] = adjDir.y; pd[2 * aa.rdC] = adjDir.z;
+        }
+      }
+    }
+  }
+
+  if constexpr (TFACC != kTfAccNone) {
+    if constexpr (TFACC == kTfAccReg) {
+      constexpr int NREG = TfGrad<TF, TFACC>::NREG;
+#pragma unroll
+      for (int e = 0; e < NREG; ++e) {
+        if (e < entries) {  // uniform
+          const float v = warp_sum(tfg.g[e]);
+          if (lane == 0 && v != 0.f) atomicAdd(s_acc + e, v);
+        }
+      }
+    } else {
+      tfg.flush_rows();
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < entries; e += blockDim.x) {
+      float v = 0.f;
+#pragma unroll
+      for (int w = 0; w < NTAB; ++w) v += s_acc[w * entries + e];
+      const int r = e / CH, c = e - r * CH;
+      if (v != 0.f) atomicAdd(aa.adjTf + b * aa.atB + r * aa.atR + c * aa.atC, v);
+    }
+  }
+}
+
+}  // namespace dvr

@@ -1,0 +1,59 @@
+// Host-visible launchers of the precompiled sm_100a kernel instances. They replace the
+// reference's NVRTC kernel loader (renderer/kernel_loader.cpp:193-261,356-457): the
+// (filter, tf, blend, flags) tuple selects an instance from a static switch instead of
+// assembling a template-name string and compiling it at run time.
+#pragma once
+#include <cuda_runtime.h>
+#include "dvr_params.h"
+
+namespace dvr {
+
+// returns cudaErrorInvalidValue if the combination has no instance
+cudaError_t launch_forward(int filter, int tf, int blend, const RayInputs& in, const ForwardOutputs& out,
+                           dim3 grid, size_t smem, cudaStream_t stream);
+
+// tfacc: 0 none, 1 register accumulators, 2 shared-memory tables (see dvr_kernels.cuh)
+cudaError_t launch_adjoint(int filter, int tf, int blend, bool hasVol, int tfacc, bool hasRay,
+                           const RayInputs& in, const AdjointArgs& aa, dim3 grid, size_t smem,
+                           cudaStream_t stream);
+
+// chunk: number of tangent slots per pass (1, 6 or 8)
+cudaError_t launch_forward_gradients(int filter, int tf, int blend, int chunk, bool hasPos, bool hasTf,
+                                     const RayInputs& in, const ForwardOutputs& out,
+                                     const ForwardGradArgs& ga, dim3 grid, size_t smem,
+                                     cudaStream_t stream);
+
+cudaError_t launch_fwdvars_to_gradients(const FwdVarsArgs& a, cudaStream_t stream);
+
+cudaError_t launch_count_cells(const RayInputs& in, const int* term, long long tB, long long tY, long long tX,
+                               unsigned long long* counts, dim3 grid, cudaStream_t stream);
+
+// per-(tf, blend) translation units (parallel compilation)
+#define DVR_DECL_ADJ(TF, BL)                                                                          \
+  cudaError_t launch_adjoint_##TF##_##BL(int filter, bool hasVol, int tfacc, bool hasRay,             \
+                                         const RayInputs& in, const AdjointArgs& aa, dim3 grid,       \
+                                         size_t smem, cudaStream_t stream);
+DVR_DECL_ADJ(0, 0) DVR_DECL_ADJ(0, 1) DVR_DECL_ADJ(1, 0) DVR_DECL_ADJ(1, 1) DVR_DECL_ADJ(2, 0)
+DVR_DECL_ADJ(2, 1) DVR_DECL_ADJ(3, 0) DVR_DECL_ADJ(3, 1) DVR_DECL_ADJ(6, 0) DVR_DECL_ADJ(6, 1)
+#undef DVR_DECL_ADJ
+#define DVR_DECL_FG(TF, BL)                                                                           \
+  cudaError_t launch_fwdgrad_##TF##_##BL(int filter, int chunk, bool hasPos, bool hasTf,              \
+                                         const RayInputs& in, const ForwardOutputs& out,              \
+                                         const ForwardGradArgs& ga, dim3 grid, size_t smem,           \
+                                         cudaStream_t stream);
+DVR_DECL_FG(0, 0) DVR_DECL_FG(0, 1) DVR_DECL_FG(1, 0) DVR_DECL_FG(1, 1) DVR_DECL_FG(2, 0)
+DVR_DECL_FG(2, 1) DVR_DECL_FG(3, 0) DVR_DECL_FG(3, 1)
+#undef DVR_DECL_FG
+
+template <typename K, typename... Args>
+inline cudaError_t launch_kernel(K kernel, dim3 grid, int threads, size_t smem, cudaStream_t stream,
+                                 const Args&... args) {
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    if (e != cudaSuccess) return e;
+  }
+  kernel<<<grid, threads, smem, stream>>>(args...);
+  return cudaGetLastError();
+}
+
+}  // namespace dvr

@@ -1,0 +1,97 @@
+// Forward-variables -> gradients kernel instance and launcher.
+#include "dvr_fwdgrad.cuh"
+#include "dvr_launch.h"
+
+namespace dvr {
+
+// ===============================================================================================
+// forward variables -> gradients (renderer_kernels.cuh:504-561): per pixel <adjColor, J[:,d,:]>;
+// stepsize / camera adjoints are STORED, TF adjoints are summed over all pixels. The TF sum is
+// pre-reduced per warp (shuffle) and per CTA (shared memory) before R*C global atomics per CTA
+// (the reference issues R*C global atomics per PIXEL).
+// ===============================================================================================
+__global__ void __launch_bounds__(256) k_fwdvars_to_gradients(const FwdVarsArgs a) {
+  extern __shared__ float s_acc[];  // R*C
+  const int entries = a.hasTf ? a.R * a.C : 0;
+  for (int i = threadIdx.x; i < entries; i += blockDim.x) s_acc[i] = 0.f;
+  __syncthreads();
+  const int b = blockIdx.z;
+  const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool active = pix < (long long)a.W * a.H;
+  const int y = active ? int(pix / a.W) : 0, x = active ? int(pix - (long long)y * a.W) : 0;
+  f4 g = {0.f, 0.f, 0.f, 0.f};
+  const float* fv = a.fv + b * a.fB + y * a.fY + x * a.fX;
+  if (active) {
+    const float* gp = a.gradColor.p + b * a.gradColor.b + y * a.gradColor.y + x * a.gradColor.x;
+    g = {__ldg(gp), __ldg(gp + a.gradColor.c), __ldg(gp + 2 * a.gradColor.c), __ldg(gp + 3 * a.gradColor.c)};
+  }
+  auto contract = [&](int d) {
+    const float* p = fv + d * a.fD;
+    return g.x * __ldg(p) + g.y * __ldg(p + a.fC) + g.z * __ldg(p + 2 * a.fC) + g.w * __ldg(p + 3 * a.fC);
+  };
+  if (active) {
+    if (a.dStep >= 0) a.adjStep[b * a.asB + y * a.asY + x * a.asX] = contract(a.dStep);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      if (a.dRayStart[c] >= 0) a.adjRayStart[b * a.rsB + y * a.rsY + x * a.rsX + c * a.rsC] = contract(a.dRayStart[c]);
+      if (a.dRayDir[c] >= 0) a.adjRayDir[b * a.rdB + y * a.rdY + x * a.rdX + c * a.rdC] = contract(a.dRayDir[c]);
+    }
+  }
+  if (a.hasTf) {
+    const int lane = threadIdx.x & 31;
+    for (int e = 0; e < entries; ++e) {  // uniform loop, all lanes take part in the shuffles
+      const int r = e / a.C, c = e - r * a.C;
+      const int d = __ldg(a.dTf + b * a.dtB + r * a.dtR + c * a.dtC);
+      if (d < 0) continue;  // uniform
+      const float v = warp_sum(active ? contract(d) : 0.f);
+      if (lane == 0 && v != 0.f) atomicAdd(s_acc + e, v);
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < entries; e += blockDim.x) {
+      const int r = e / a.C, c = e - r * a.C;
+      if (s_acc[e] != 0.f) atomicAdd(a.adjTf + b * a.atB + r * a.atR + c * a.atC, s_acc[e]);
+    }
+  }
+}
+
+// counts samples and cell visits of every ray (measurement utility, see dvr_count_cell_visits)
+__global__ void __launch_bounds__(kThreads) k_count_cells(const RayInputs in, const int* term, long long tB,
+                                                          long long tY, long long tX, unsigned long long* counts) {
+  int x, y;
+  thread_pixel(x, y);
+  const int b = blockIdx.z;
+  unsigned ns = 0, nc = 0;
+  if (x < in.W && y < in.H) {
+    const Ray ray = make_ray(in, x, y, b);
+    const int n = __ldg(term + b * tB + y * tY + x * tX);
+    int kx = -1, ky = -1, kz = -1;
+    float fi = 0.f;
+    for (int i = 0; i < n; ++i, fi += 1.0f) {
+      const float t = sample_t(ray, fi);
+      const int cx = __float_as_int(biased_trunc(fmaf(t, ray.pd.x, ray.ps.x)));
+      const int cy = __float_as_int(biased_trunc(fmaf(t, ray.pd.y, ray.ps.y)));
+      const int cz = __float_as_int(biased_trunc(fmaf(t, ray.pd.z, ray.ps.z)));
+      if (cx != kx || cy != ky || cz != kz) { ++nc; kx = cx; ky = cy; kz = cz; }
+    }
+    ns = unsigned(n);
+  }
+  const unsigned ws = __reduce_add_sync(0xffffffffu, ns), wc = __reduce_add_sync(0xffffffffu, nc);
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(counts, (unsigned long long)ws);
+    atomicAdd(counts + 1, (unsigned long long)wc);
+  }
+}
+
+cudaError_t launch_count_cells(const RayInputs& in, const int* term, long long tB, long long tY, long long tX,
+                               unsigned long long* counts, dim3 grid, cudaStream_t s) {
+  return launch_kernel(k_count_cells, grid, kThreads, 0, s, in, term, tB, tY, tX, counts);
+}
+
+cudaError_t launch_fwdvars_to_gradients(const FwdVarsArgs& a, cudaStream_t s) {
+  const long long pixels = (long long)a.W * a.H;
+  const dim3 grid((unsigned)((pixels + 255) / 256), 1, a.B);
+  const size_t smem = size_t(a.hasTf ? a.R * a.C : 0) * sizeof(float);
+  return launch_kernel(k_fwdvars_to_gradients, grid, 256, smem, s, a);
+}
+
+}  // namespace dvr

@@ -1,0 +1,112 @@
+// Kernel-argument PODs shared by the host dispatch (dvr_capi.cpp) and the sm_100a kernels.
+// They replace the reference's by-value accessor structs (kernel::RendererInputs & co,
+// renderer/renderer_settings.cuh:150-244): strides are pre-resolved on the host (size-1
+// dimensions -> stride 0, renderer/renderer_tensor.cuh:140-144), scalar variants travel by
+// value, and the reference-frame tangents are computed once on the host.
+#pragma once
+#include <stdint.h>
+
+namespace dvr {
+
+// tile geometry: one warp = 8x4 pixels, one CTA = 2x2 warps = 16x8 pixels
+constexpr int kWarpW = 8, kWarpH = 4;
+constexpr int kCtaW = 16, kCtaH = 8;
+constexpr int kThreads = 128;
+
+// numeric enum values of renderer/renderer_settings.cuh:81-146
+enum : int { kFilterNearest = 0, kFilterTrilinear = 1, kFilterPreshaded = 3 };
+enum : int { kCamRays = 0, kCamInvView = 1, kCamFrame = 2 };
+enum : int { kTfIdentity = 0, kTfTexture = 1, kTfLinear = 2, kTfGaussian = 3, kTfPreshaded = 5, kTfGaussianLog = 6 };
+enum : int { kBlendBeer = 0, kBlendAlpha = 1 };
+
+struct Strided1 { const float* p; long long b, c; };             // (B)*3
+struct Strided3 { const float* p; long long b, y, x; };          // (B)*(H)*(W)
+struct Strided4 { const float* p; long long b, y, x, c; };       // (B)*H*W*3|4
+struct StridedMat { const float* p; long long b, r, c; };        // (B)*R*C
+
+struct RayInputs {
+  int W, H, B;
+  int X, Y, Z;                       // volume resolution
+  // volume, element offsets: base + b*volB + x*sx + y*sy + z*sz (per-batch span < 2^31)
+  const float* volume;
+  long long volB;
+  int sx, sy, sz;
+  Strided1 boxMin, boxSize;          // p == nullptr -> use the *V value
+  float boxMinV[3], boxSizeV[3];
+  int cameraMode;
+  Strided4 rayStart, rayDir;         // kCamRays
+  StridedMat camMat;                 // kCamInvView (4x4) / kCamFrame (3x3); p == nullptr -> camMatV
+  float camMatV[16];
+  float tanFovX, tanFovY;            // kCamFrame, computed on the host (tanf of the half angles)
+  Strided3 stepSize;                 // p == nullptr -> stepV
+  float stepV;
+  StridedMat tf;                     // (B)*R*C
+  int R, C;
+  float earlyOut;
+};
+
+struct ForwardOutputs {
+  float* color;                      // B*H*W*4
+  long long cB, cY, cX, cC;
+  int colorVec4;                     // 1: cC==1, 16-byte aligned rows -> one STG.128 per pixel
+  int* term;                         // B*H*W
+  long long tB, tY, tX;
+};
+
+struct AdjointArgs {
+  // outputs of the forward pass + adjoint colour
+  Strided4 color;                    // (B)*H*W*4
+  const int* term;
+  long long tB, tY, tX;
+  Strided4 adjColor;
+  // outputs (accumulated)
+  float* adjVolume;                  // element offsets like the volume
+  long long avB;
+  int avx, avy, avz;
+  float* adjStep;
+  long long asB, asY, asX;
+  int stepAtomic;                    // broadcasting -> atomics (renderer_kernels.cuh:418-421)
+  float* adjRayStart;
+  long long rsB, rsY, rsX, rsC;
+  float* adjRayDir;
+  long long rdB, rdY, rdX, rdC;
+  int camAtomic;
+  float* adjTf;
+  long long atB, atR, atC;
+  int hasStep, hasCam;
+  int compatStepOverwrite;           // see include/dvr_b200.h
+};
+
+struct ForwardGradArgs {
+  int D;                             // total number of tangents
+  int d0;                            // first tangent slot handled by this pass
+  int writeColor;                    // only the first pass writes colour / terminationIndex
+  int dStep;
+  int dRayStart[3], dRayDir[3];
+  const int* dTf;                    // (B)*R*C slots or nullptr
+  long long dtB, dtR, dtC;
+  float* grad;                       // B*H*W*D*4
+  long long gB, gY, gX, gD, gC;
+};
+
+struct FwdVarsArgs {
+  int W, H, B, D;
+  const float* fv;                   // B*H*W*D*4
+  long long fB, fY, fX, fD, fC;
+  Strided4 gradColor;
+  int dStep;
+  int dRayStart[3], dRayDir[3];
+  const int* dTf;
+  long long dtB, dtR, dtC;
+  int R, C, hasTf;
+  float* adjStep;
+  long long asB, asY, asX;
+  float* adjRayStart;
+  long long rsB, rsY, rsX, rsC;
+  float* adjRayDir;
+  long long rdB, rdY, rdX, rdC;
+  float* adjTf;
+  long long atB, atR, atC;
+};
+
+}  // namespace dvr

@@ -36,6 +36,12 @@ extern "C" {
 
 #define DVR_MAX_DIMS 5
 
+#if defined(__GNUC__)
+#define DVR_API __attribute__((visibility("default")))
+#else
+#define DVR_API
+#endif
+
 /* error codes */
 #define DVR_OK 0
 #define DVR_ERR_INVALID_ARGUMENT (-1) /* shape / enum / flag validation failed      */
@@ -143,37 +149,45 @@ typedef struct DvrAdjointOutputs {
 
 /* RendererCuda::renderForward (renderer/renderer_cuda.cpp:85-118) ->
  * DvrKernelForwardDevice (renderer/renderer_kernels.cuh:92-106). */
-int dvr_render_forward(const DvrInputs* inputs, const DvrOutputs* outputs, void* stream);
+DVR_API int dvr_render_forward(const DvrInputs* inputs, const DvrOutputs* outputs, void* stream);
 
 /* RendererCuda::renderForwardGradients (renderer/renderer_cuda.cpp:120-183) ->
  * DvrKernelForwardGradientsDevice (renderer/renderer_kernels.cuh:258-279).
  * gradients_out: B*H*W*D*4 fp32. */
-int dvr_render_forward_gradients(const DvrInputs* inputs,
+DVR_API int dvr_render_forward_gradients(const DvrInputs* inputs,
                                  const DvrForwardDifferencesSettings* settings,
                                  const DvrOutputs* outputs, const DvrTensor* gradients_out,
                                  void* stream);
 
 /* RendererCuda::forwardVariablesToGradients (renderer/renderer_cuda.cpp:185-224) ->
  * ForwardVariablesToGradientsDevice (renderer/renderer_kernels.cuh:564-576). */
-int dvr_forward_variables_to_gradients(const DvrTensor* forward_variables,
+DVR_API int dvr_forward_variables_to_gradients(const DvrTensor* forward_variables,
                                        const DvrTensor* grad_output_color,
                                        const DvrForwardDifferencesSettings* settings,
                                        const DvrAdjointOutputs* adj_outputs, void* stream);
 
 /* RendererCuda::renderAdjoint (renderer/renderer_cuda.cpp:226-317) ->
  * DvrKernelAdjointDevice (renderer/renderer_kernels.cuh:447-468). */
-int dvr_render_adjoint(const DvrInputs* inputs, const DvrOutputs* outputs_from_forward,
+DVR_API int dvr_render_adjoint(const DvrInputs* inputs, const DvrOutputs* outputs_from_forward,
                        const DvrTensor* adj_color, const DvrAdjointOutputs* adj_outputs,
                        void* stream);
+
+/* Measurement utility (bench accounting): re-walks every ray up to its
+ * terminationIndex and counts samples and CELL VISITS (a sample whose integer cell differs
+ * from the ray's previous one -- the unit the reference's cell cache reloads 8 corners for,
+ * renderer/renderer_interpolation.cuh:221,337). counts = device pointer to 2 uint64
+ * {N_samples, N_cells}, accumulated (caller zeroes). */
+DVR_API int dvr_count_cell_visits(const DvrInputs* inputs, const DvrTensor* termination_index,
+                                  uint64_t* counts, void* stream);
 
 /* Computes the broadcast batch size and volume resolution exactly like
  * Renderer::checkInputs (renderer/renderer.cpp:49-263); validates shapes.
  * Any out pointer may be NULL. */
-int dvr_check_inputs(const DvrInputs* inputs, int32_t* B, int32_t* X, int32_t* Y, int32_t* Z);
+DVR_API int dvr_check_inputs(const DvrInputs* inputs, int32_t* B, int32_t* X, int32_t* Y, int32_t* Z);
 
 /* 1 if the (filter, camera, tf, blend) combination has a precompiled instance, else 0.
  * Replaces "does it compile under NVRTC" (unittests/testCudaCompilation.cpp:109-287). */
-int dvr_has_variant(int32_t volume_filter_mode, int32_t camera_mode, int32_t tf_mode,
+DVR_API int dvr_has_variant(int32_t volume_filter_mode, int32_t camera_mode, int32_t tf_mode,
                     int32_t blend_mode);
 
 /* Runtime options (replace Renderer::setCudaSyncMode etc., renderer/renderer.h:128-150,
@@ -189,17 +203,17 @@ int dvr_has_variant(int32_t volume_filter_mode, int32_t camera_mode, int32_t tf_
  *                               1 = re-brick into the internal tiled layout per call,
  *                               -1 (default) = automatic
  * Returns DVR_OK or DVR_ERR_INVALID_ARGUMENT for an unknown name. */
-int dvr_set_option(const char* name, int32_t value);
-int dvr_get_option(const char* name, int32_t* value);
+DVR_API int dvr_set_option(const char* name, int32_t value);
+DVR_API int dvr_get_option(const char* name, int32_t* value);
 
 /* Number of kernel launches issued by this library since load (for bench accounting). */
-int64_t dvr_launch_count(void);
+DVR_API int64_t dvr_launch_count(void);
 
 /* Thread-local description of the last error returned on this thread ("" if none). */
-const char* dvr_last_error(void);
+DVR_API const char* dvr_last_error(void);
 
 /* ABI version of this header. */
-int32_t dvr_abi_version(void);
+DVR_API int32_t dvr_abi_version(void);
 #define DVR_ABI_VERSION 1
 
 #ifdef __cplusplus

@@ -206,3 +206,29 @@ def symmetric_error(a, b):
     a = np.asarray(a, dtype=np.float64)
     b = np.asarray(b, dtype=np.float64)
     return float(np.max(np.abs(a - b) / np.maximum(1.0, np.abs(a) + np.abs(b)))) if a.size else 0.0
+
+
+def per_ray_errors(got, want):
+    """Per-ray error of a per-ray quantity (leading dims B,H,W), normalised by the RMS per-ray
+    magnitude of ``want``. Quantities that contain d(trilinear)/d(position) are DISCONTINUOUS across
+    cell faces, so a sample that lands within round-off of a face flips the term for that ray in any
+    fp32 implementation (the reference's fp32 and fp64 builds disagree on such rays too); robust
+    statistics over rays (median, outlier fraction) separate that from systematic error."""
+    got = np.asarray(got, dtype=np.float64)
+    want = np.asarray(want, dtype=np.float64)
+    n = got.shape[0] * got.shape[1] * got.shape[2]
+    g, w = got.reshape(n, -1), want.reshape(n, -1)
+    scale = np.sqrt(np.mean(np.sum(w * w, axis=1)))
+    return np.sqrt(np.sum((g - w) ** 2, axis=1)) / (scale if scale > 0 else 1.0)
+
+
+def assert_position_gradient_close(name, got, want32, want64, tol=1e-4):
+    """rel-L2 <= tol against the fp32 oracle, or -- when cell-face flips make the fp32 oracle itself
+    deviate from the fp64 oracle -- no worse than the fp32 oracle in median and in outlier fraction."""
+    if rel_l2(got, want32) <= tol:
+        return
+    e_got, e_ref = per_ray_errors(got, want64), per_ray_errors(want32, want64)
+    med_got, med_ref = np.median(e_got), np.median(e_ref)
+    out_got, out_ref = np.mean(e_got > 10 * tol), np.mean(e_ref > 10 * tol)
+    assert med_got <= max(tol / 10, 2 * med_ref), f"{name}: median per-ray error {med_got:.2e} (fp32 oracle {med_ref:.2e})"
+    assert out_got <= max(0.02, 2 * out_ref), f"{name}: outlier rays {out_got:.3f} (fp32 oracle {out_ref:.3f})"
