@@ -880,6 +880,40 @@ static void forward_variables_to_gradients(const DvrTensor& fvT, const DvrTensor
   }
 }
 
+// ---- test diagnostic: distance of a ray's samples to the nearest cell face --------------------------
+// d(trilinear)/d(position) is discontinuous where the integer cell changes (renderer_interpolation.cuh
+// :221-228: ipos = int(volumePos), corners clamped to size-1), i.e. at integer coordinates 1..size-1 of
+// every axis. A sample within round-off of such a face flips cells between ANY two fp32 evaluation
+// orders (the reference's own fp32 and fp64 builds disagree on such rays; rays that enter the box
+// through a "max" face always start exactly on one). The parity tests use this per-ray minimum (in
+// voxels, over the samples 0..terminationIndex-1) to separate face-sensitive rays from the rest.
+template <typename R>
+static void face_distance(const DvrInputs& in, const DvrTensor& termT, const DvrTensor& outT) {
+  Scene<R> s(in);
+  View<int32_t> term(termT, 3);
+  View<R> out(outT, 3, false);
+  const int64_t count = int64_t(s.W) * s.H * s.B;
+  const int size[3] = {s.X, s.Y, s.Z};
+#pragma omp parallel for schedule(guided)
+  for (int64_t idx = 0; idx < count; ++idx) {
+    const int b = int(idx / (int64_t(s.W) * s.H));
+    const int y = int((idx - int64_t(b) * s.W * s.H) / s.W);
+    const int x = int(idx - int64_t(s.W) * (y + int64_t(s.H) * b));
+    const Ray<R> r = setup_ray(s, x, y, b);
+    const int n = term.at(b, y, x);
+    R best = R(1);
+    for (int i = 0; i < n; ++i) {
+      const V3<R> p = volume_pos(r, r.tmin + i * r.step);
+      const R pc[3] = {p.x, p.y, p.z};
+      for (int a = 0; a < 3; ++a) {
+        const R k = clampr(std::round(pc[a]), R(1), R(size[a] - 1));
+        best = rmin(best, std::abs(pc[a] - k));
+      }
+    }
+    out.at(b, y, x) = best;
+  }
+}
+
 template <typename F>
 static int guarded(F&& f) {
   try {
@@ -914,6 +948,9 @@ using namespace dvro;
                                           const DvrTensor* ac, const DvrAdjointOutputs* ao,        \
                                           void*) {                                                  \
     return guarded([&] { render_adjoint<R>(*i, *f, *ac, *ao); });                                   \
+  }                                                                                                 \
+  extern "C" int dvro##P##_face_distance(const DvrInputs* i, const DvrTensor* t, const DvrTensor* o) { \
+    return guarded([&] { face_distance<R>(*i, *t, *o); });                                          \
   }                                                                                                 \
   extern "C" const char* dvro##P##_last_error() { return g_error.c_str(); }                         \
   extern "C" int dvro##P##_real_size() { return int(sizeof(R)); }

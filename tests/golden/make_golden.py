@@ -1,0 +1,44 @@
+#!/usr/bin/env python
+"""Generates the golden fixtures under tests/golden/ from the REFERENCE ITSELF.
+
+Run in the build container (needs /root/reference and `make -C oracle ref`):
+
+    python tests/golden/make_golden.py
+
+* ``ref_*.npz``: outputs of the reference's own OpenMP host kernels (oracle/_ref/libdvr_ref32.so =
+  DvrKernelForwardHost / DvrKernelAdjointHost / DvrKernelForwardGradientsHost of
+  renderer/renderer_kernels.cuh compiled unmodified from /root/reference; the forward-mode kernel is
+  instantiated over the restated cudAD of oracle/cudad_restated) on the seeded scenes of
+  tests/scenes.py. The scene INPUTS are regenerated from the seed by the tests; only the outputs are
+  stored.
+* ``NonConvexDensity.tsv``: copied verbatim from /root/reference/unittests/NonConvexDensity.tsv
+  (the reference's committed known-answer table, generator unittests/testNonConvexDensity.cpp:8-80).
+"""
+import os
+import shutil
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+import golden_cases  # noqa: E402
+import oracle_loader as ol  # noqa: E402
+import scenes  # noqa: E402
+
+
+def main():
+    ref = ol.ref(32)
+    assert ref is not None, "oracle/_ref/libdvr_ref32.so missing: run `make -C oracle ref`"
+    for name, sc, flags, fg in golden_cases.cases():
+        out = golden_cases.run(ref, sc, flags, fg)
+        np.savez_compressed(os.path.join(HERE, f"ref_{name}.npz"), **out)
+        print(name, {k: v.shape for k, v in out.items()})
+    src = "/root/reference/unittests/NonConvexDensity.tsv"
+    if os.path.exists(src):
+        shutil.copyfile(src, os.path.join(HERE, "NonConvexDensity.tsv"))
+
+
+if __name__ == "__main__":
+    main()

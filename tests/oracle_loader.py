@@ -39,6 +39,17 @@ class OracleLibrary(capi.Library):
             f.restype = ctypes.c_int
             f.argtypes = [ctypes.c_double, ctypes.POINTER(ctypes.c_double)]
 
+        f = getattr(self.lib, prefix + "face_distance", None)
+        if f is not None:
+            f.restype = ctypes.c_int
+            f.argtypes = [ctypes.POINTER(capi.DvrInputs), ctypes.POINTER(capi.DvrTensor),
+                          ctypes.POINTER(capi.DvrTensor)]
+
+    def face_distance(self, inputs, termination_index, out):
+        """Per-ray minimum distance (voxels) of the samples to a trilinear cell face (port only)."""
+        ci, t, o = inputs.to_c(), capi.tensor_view(termination_index), capi.tensor_view(out)
+        self._check(getattr(self.lib, self.prefix + "face_distance")(ci, t, o))
+
     def nonconvex_density(self, d1: float):
         out = (ctypes.c_double * 4)()
         self._check(getattr(self.lib, self.prefix + "nonconvex_density")(d1, out))

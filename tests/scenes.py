@@ -222,13 +222,47 @@ def per_ray_errors(got, want):
     return np.sqrt(np.sum((g - w) ** 2, axis=1)) / (scale if scale > 0 else 1.0)
 
 
-def assert_position_gradient_close(name, got, want32, want64, tol=1e-4):
-    """rel-L2 <= tol against the fp32 oracle, or -- when cell-face flips make the fp32 oracle itself
-    deviate from the fp64 oracle -- no worse than the fp32 oracle in median and in outlier fraction."""
+FACE_EPS = 3e-5  # voxels; ~8x the fp32 round-off of a sample coordinate on a <=64^3 test volume
+
+
+def face_sensitive_rays(scene: Scene, term, eps=FACE_EPS):
+    """Boolean (B,H,W) mask of rays with a sample within ``eps`` voxels of a trilinear cell face
+    (computed in fp64 by the oracle's diagnostic, oracle/dvr_oracle.cpp face_distance)."""
+    import oracle_loader as ol
+    if scene.filter_mode != capi.FILTER_TRILINEAR:
+        return np.zeros(term.shape, dtype=bool)
+    fd = np.ones(term.shape, dtype=np.float64)
+    inp = scene.inputs(lambda a: a.astype(np.float64) if a.dtype != np.int32 else a)
+    ol.port(64).face_distance(inp, np.ascontiguousarray(term, dtype=np.int32), fd)
+    return fd < eps
+
+
+def assert_position_gradient_close(name, got, want32, want64, tol=1e-4, sensitive=None):
+    """Per-ray quantities that contain d(trilinear)/d(position): rel-L2 <= tol against the fp32
+    oracle over all rays, or -- because that derivative is DISCONTINUOUS across cell faces, so a
+    sample within round-off of a face (always the case for the first sample of a ray that enters
+    through a max face of the box) takes either side in any fp32 evaluation order, the reference's
+    own fp32 and fp64 builds included --
+      * on the rays WITHOUT such a sample (``sensitive`` False): rel-L2 <= tol against the fp64
+        oracle, or no further from it than 1.5x the fp32 oracle is;
+      * on the face-sensitive rays: median per-ray error no worse than 2x the fp32 oracle's and
+        every ray within the size of one flipped sample (half the RMS ray gradient)."""
     if rel_l2(got, want32) <= tol:
         return
-    e_got, e_ref = per_ray_errors(got, want64), per_ray_errors(want32, want64)
-    med_got, med_ref = np.median(e_got), np.median(e_ref)
-    out_got, out_ref = np.mean(e_got > 10 * tol), np.mean(e_ref > 10 * tol)
-    assert med_got <= max(tol / 10, 2 * med_ref), f"{name}: median per-ray error {med_got:.2e} (fp32 oracle {med_ref:.2e})"
-    assert out_got <= max(0.02, 2 * out_ref), f"{name}: outlier rays {out_got:.3f} (fp32 oracle {out_ref:.3f})"
+    assert sensitive is not None, f"{name}: rel-L2 {rel_l2(got, want32):.2e} > {tol} and no face mask given"
+    lead = sensitive.shape
+    g = np.asarray(got, dtype=np.float64).reshape(lead + (-1,))
+    w32 = np.asarray(want32, dtype=np.float64).reshape(lead + (-1,))
+    w64 = np.asarray(want64, dtype=np.float64).reshape(lead + (-1,))
+    ok = ~sensitive
+    if ok.any():
+        e_got, e_ref = rel_l2(g[ok], w64[ok]), rel_l2(w32[ok], w64[ok])
+        assert e_got <= max(tol, 1.5 * e_ref), (
+            f"{name}: rel-L2 on face-insensitive rays {e_got:.2e} (fp32 oracle {e_ref:.2e}, {ok.mean():.2f} of rays)")
+    if sensitive.any():
+        e_got, e_ref = per_ray_errors(got, want64), per_ray_errors(want32, want64)
+        m = sensitive.reshape(-1)
+        med_got, med_ref = np.median(e_got[m]), np.median(e_ref[m])
+        assert med_got <= max(tol / 10, 2 * med_ref), (
+            f"{name}: median error on face-sensitive rays {med_got:.2e} (fp32 oracle {med_ref:.2e})")
+        assert e_got[m].max() <= 0.5, f"{name}: face-sensitive ray off by {e_got[m].max():.2e} of the RMS gradient"

@@ -2,11 +2,12 @@
 the same seeded inputs.
 
 Tolerances (BASELINE.json north_star): relative L2 <= 1e-5 on images, <= 1e-4 on gradients.
-Where the fp32 REFERENCE itself is further than that from its own fp64 build (the reference's
-positional adjoint subtracts two corner sums of similar size, renderer_interpolation.cuh:368-386,
-which makes its fp32 camera gradients noisy at the 1e-3 level), the criterion is the one the
-reference authors imply by running their suite in fp64 (unittests/main.cpp:22-24): the CUDA
-result must be at least as close to the fp64 oracle as the fp32 oracle is.
+Per-ray camera / stepsize gradients contain d(trilinear)/d(position), which is discontinuous across
+cell faces; rays with a sample within round-off of a face (every ray that enters the box through a
+max face starts on one) are identified with the oracle's fp64 face-distance diagnostic and judged
+against the fp64 oracle relative to what the fp32 oracle itself achieves there -- the reference
+authors run their own suite in fp64 for the same reason (unittests/main.cpp:22-24). All other rays,
+and every other gradient, must meet the tolerance outright (see scenes.assert_position_gradient_close).
 """
 import numpy as np
 import pytest
@@ -52,9 +53,10 @@ def run_case(oracles, sc, *, volume=True, step=True, camera=True, tf=True, delay
     w32 = scenes.np_adjoint(o32, sc, want_c, want_t, adj_color, **kw)
     w64 = scenes.np_adjoint(o64, sc, want_c.astype(np.float64), want_t, adj_color.astype(np.float64),
                             dtype=np.float64, **kw)
+    sens = scenes.face_sensitive_rays(sc, want_t) if (step or camera) else None
     for k in w32:
         if k in ("adj_camera_ray_start", "adj_camera_ray_dir", "adj_step_size") and w32[k].shape[:3] == want_t.shape:
-            scenes.assert_position_gradient_close(k, got[k], w32[k], w64[k], GRAD_TOL)
+            scenes.assert_position_gradient_close(k, got[k], w32[k], w64[k], GRAD_TOL, sens)
         else:
             check_grad(k, got[k], w32[k], w64[k])
     return got
