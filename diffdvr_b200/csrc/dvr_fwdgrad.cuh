@@ -164,8 +164,8 @@ __global__ void __launch_bounds__(kThreads) k_forward_gradients(const RayInputs 
     const float t = sample_t(ray, fi);
     if (t > ray.tmax) break;
     if (acc.w.v > in.earlyOut) break;
-    const float px = fmaf(t, ray.pd.x, ray.ps.x), py = fmaf(t, ray.pd.y, ray.ps.y), pz = fmaf(t, ray.pd.z, ray.ps.z);
-    const float density = smp.fetch(in, nullptr, px, py, pz);
+    const f3 p = sample_pos<HAS_POS>(ray, t);
+    const float density = smp.fetch(in, nullptr, p.x, p.y, p.z);
     Du4<N> cur;
     Du<N> alpha;
     if constexpr (HAS_POS) {

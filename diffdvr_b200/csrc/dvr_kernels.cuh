@@ -281,8 +281,8 @@ __global__ void __launch_bounds__(kThreads) k_adjoint(const RayInputs in, const 
     float fi = float(n - 1);
     for (int i = n - 1; i >= 0; --i, fi -= 1.0f) {
       const float t = sample_t(ray, fi);
-      const float density = smp.fetch(in, &aa, fmaf(t, ray.pd.x, ray.ps.x), fmaf(t, ray.pd.y, ray.ps.y),
-                                      fmaf(t, ray.pd.z, ray.ps.z));
+      const f3 p = sample_pos<HAS_RAY>(ray, t);
+      const float density = smp.fetch(in, &aa, p.x, p.y, p.z);
       const f4 cur = tf_eval<TF>(s_tf, in.R, density);
       f4 adjCur;
       float adjStepBlend;
