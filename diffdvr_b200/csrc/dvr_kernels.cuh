@@ -26,17 +26,35 @@ __global__ void __launch_bounds__(kThreads) k_forward(const RayInputs in, const 
   Sampler<FILTER, false> smp;
   smp.init(in, b, nullptr, 0);
   f4 acc = {0.f, 0.f, 0.f, 0.f};
-  int i = 0;
-  float fi = 0.f;
-  for (;; ++i, fi += 1.0f) {
-    const float t = sample_t(ray, fi);
-    if (t > ray.tmax) break;
-    if (acc.w > in.earlyOut) break;
-    const float density = smp.fetch(in, nullptr, fmaf(t, ray.pd.x, ray.ps.x), fmaf(t, ray.pd.y, ray.ps.y),
-                                    fmaf(t, ray.pd.z, ray.ps.z));
-    const f4 cur = tf_eval<TF>(smem, in.R, density);
-    acc = blend_over(acc, cur, blend_alpha<BLEND>(cur.w, ray.step));
+  float fi = 0.f;  // sample counter; exact in fp32 (terminationIndex < 2^24)
+  if constexpr (TF == kTfIdentity) {
+    // r = g = b for this TF (renderer_tf.cuh:62-73): march one colour channel; the table's two
+    // scales stay in registers
+    const float sa = smem[0], sc = smem[1];
+    for (;; fi += 1.0f) {
+      const float t = sample_t(ray, fi);
+      if (t > ray.tmax) break;
+      if (acc.w > in.earlyOut) break;
+      const f3 p = sample_pos<false>(ray, t);
+      const float dc = fmaxf(0.f, fminf(smp.fetch(in, nullptr, p.x, p.y, p.z), 1.f));
+      const float alpha = blend_alpha<BLEND>(dc * sa, ray.step);
+      const float om = 1.f - acc.w;
+      acc.x = fmaf(om * (dc * sc), alpha, acc.x);
+      acc.w = fmaf(om, alpha, acc.w);
+    }
+    acc.y = acc.z = acc.x;
+  } else {
+    for (;; fi += 1.0f) {
+      const float t = sample_t(ray, fi);
+      if (t > ray.tmax) break;
+      if (acc.w > in.earlyOut) break;
+      const f3 p = sample_pos<false>(ray, t);
+      const float density = smp.fetch(in, nullptr, p.x, p.y, p.z);
+      const f4 cur = tf_eval<TF>(smem, in.R, density);
+      acc = blend_over(acc, cur, blend_alpha<BLEND>(cur.w, ray.step));
+    }
   }
+  const int i = int(fi);
   float* c = out.color + b * out.cB + y * out.cY + x * out.cX;
   if (out.colorVec4) {
     *reinterpret_cast<float4*>(c) = make_float4(acc.x, acc.y, acc.z, acc.w);
