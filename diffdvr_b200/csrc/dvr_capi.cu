@@ -582,6 +582,48 @@ int dvr_get_option(const char* name, int32_t* value) {
   return DVR_ERR_INVALID_ARGUMENT;
 }
 
+int dvr_device_synchronize(void) {
+  return guarded([&] { cuda_check(cudaDeviceSynchronize(), "dvr_device_synchronize"); });
+}
+
+struct DvrTimer {
+  cudaEvent_t start, stop;
+};
+DvrTimer* dvr_timer_create(void) {
+  DvrTimer* t = new DvrTimer{nullptr, nullptr};
+  if (cudaEventCreate(&t->start) != cudaSuccess || cudaEventCreate(&t->stop) != cudaSuccess) {
+    g_error = "cudaEventCreate failed";
+    dvr_timer_destroy(t);
+    return nullptr;
+  }
+  return t;
+}
+void dvr_timer_destroy(DvrTimer* t) {
+  if (!t) return;
+  if (t->start) cudaEventDestroy(t->start);
+  if (t->stop) cudaEventDestroy(t->stop);
+  delete t;
+}
+int dvr_timer_start(DvrTimer* t, void* stream) {
+  return guarded([&] {
+    if (!t) fail(DVR_ERR_INVALID_ARGUMENT, "NULL timer");
+    cuda_check(cudaEventRecord(t->start, static_cast<cudaStream_t>(stream)), "dvr_timer_start");
+  });
+}
+int dvr_timer_stop(DvrTimer* t, void* stream) {
+  return guarded([&] {
+    if (!t) fail(DVR_ERR_INVALID_ARGUMENT, "NULL timer");
+    cuda_check(cudaEventRecord(t->stop, static_cast<cudaStream_t>(stream)), "dvr_timer_stop");
+  });
+}
+int dvr_timer_elapsed_ms(DvrTimer* t, float* ms) {
+  return guarded([&] {
+    if (!t || !ms) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    cuda_check(cudaEventSynchronize(t->stop), "dvr_timer_elapsed_ms");
+    cuda_check(cudaEventElapsedTime(ms, t->start, t->stop), "dvr_timer_elapsed_ms");
+  });
+}
+
 int64_t dvr_launch_count(void) { return g_launches.load(); }
 const char* dvr_last_error(void) { return g_error.c_str(); }
 int32_t dvr_abi_version(void) { return DVR_ABI_VERSION; }

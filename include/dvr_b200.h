@@ -209,6 +209,17 @@ DVR_API int dvr_get_option(const char* name, int32_t* value);
 /* Number of kernel launches issued by this library since load (for bench accounting). */
 DVR_API int64_t dvr_launch_count(void);
 
+/* pyrenderer.sync (bindings/bindings.cpp:306): cudaDeviceSynchronize on the current device. */
+DVR_API int dvr_device_synchronize(void);
+
+/* GPUTimer of the reference's bindings (bindings/bindings.cpp:99-129): a cudaEvent pair. */
+typedef struct DvrTimer DvrTimer;
+DVR_API DvrTimer* dvr_timer_create(void);
+DVR_API void dvr_timer_destroy(DvrTimer* timer);
+DVR_API int dvr_timer_start(DvrTimer* timer, void* stream);
+DVR_API int dvr_timer_stop(DvrTimer* timer, void* stream);
+DVR_API int dvr_timer_elapsed_ms(DvrTimer* timer, float* ms); /* waits for the stop event */
+
 /* Thread-local description of the last error returned on this thread ("" if none). */
 DVR_API const char* dvr_last_error(void);
 

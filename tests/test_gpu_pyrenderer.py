@@ -1,0 +1,120 @@
+"""GPU: the reference's Python API (`pyrenderer`, C++ host layer -> C-ABI -> sm_100a kernels) against
+the golden fixtures of the reference's compiled host kernels, against the ctypes path (same library,
+so bit-identical), plus the error behaviour and stream semantics of the reference's host layer."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import golden_cases
+import gpu_runner as gr
+import pyr_runner as pr
+import scenes
+from diffdvr_b200 import capi
+
+pytestmark = pytest.mark.gpu
+pyr = pr.pyr
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CASES = {name: (sc, flags, fg) for name, sc, flags, fg in golden_cases.cases()}
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_pyrenderer_matches_golden_reference_outputs(name):
+    sc, flags, fg = CASES[name]
+    gold = np.load(os.path.join(GOLDEN, f"ref_{name}.npz"))
+    n0 = pyr.launch_count()
+    pyr.set_option("compat_stepsize_overwrite", 1)
+    try:
+        out = golden_cases.run(None, sc, flags, fg, runner=pr, forward_from=(gold["color"], gold["term"]))
+        via_ctypes = golden_cases.run(None, sc, flags, fg, runner=gr, forward_from=(gold["color"], gold["term"]))
+    finally:
+        pyr.set_option("compat_stepsize_overwrite", 0)
+    assert pyr.launch_count() > n0                      # the CUDA library did the work
+    assert scenes.rel_l2(out["color"], gold["color"]) <= 1e-5
+    assert np.array_equal(out["color"], via_ctypes["color"]) and np.array_equal(out["term"], via_ctypes["term"])
+    for k in gold.files:
+        if k in ("adj_volume", "adj_tf"):
+            assert scenes.rel_l2(out[k], gold[k]) <= 1e-4, (k, scenes.rel_l2(out[k], gold[k]))
+        elif k.startswith("adj_"):                      # per-ray outputs: no atomics, same kernels -> identical
+            assert np.array_equal(out[k], via_ctypes[k]), k
+    if "fg_gradients" in gold.files:
+        assert np.array_equal(out["fg_gradients"], via_ctypes["fg_gradients"])
+
+
+def test_forward_variables_to_gradients_through_pyrenderer():
+    sc = scenes.make_scene(n=16, W=12, H=10, B=2, camera_mode=capi.CAMERA_RAY_START_DIR, tf_mode=capi.TF_TEXTURE,
+                           R=4, seed=5, opacity=4.0)
+    kw = dict(d_stepsize=6, d_ray_start=(0, 1, 2), d_ray_dir=(3, 4, 5))
+    _, _, fv = pr.forward_gradients(sc, 7, **kw)
+    adj_color = np.random.RandomState(3).randn(2, 10, 12, 4).astype(np.float32)
+    a = pr.forward_variables_to_gradients(fv, adj_color, 7, **kw)
+    b = gr.forward_variables_to_gradients(fv, adj_color, 7, **kw)
+    want = np.einsum("bhwc,bhwdc->bhwd", adj_color.astype(np.float64), fv.astype(np.float64))
+    assert scenes.rel_l2(a["adj_step_size"], want[..., 6]) <= 1e-6
+    assert scenes.rel_l2(a["adj_camera_ray_start"], want[..., 0:3]) <= 1e-6
+    for k in a:
+        assert np.array_equal(a[k], b[k]), k
+
+
+def test_error_behaviour_of_the_host_layer():
+    sc = scenes.make_scene(n=8, W=6, H=4, R=4)
+    inp = pr.make_inputs(sc)
+    good = pyr.RendererOutputs(torch.empty(1, 4, 6, 4, device="cuda"), torch.empty(1, 4, 6, dtype=torch.int32, device="cuda"))
+    # wrong output shape: the reference's CHECK_SIZE wording (renderer/pytorch_utils.h:9)
+    bad = pyr.RendererOutputs(torch.empty(1, 4, 5, 4, device="cuda"), good.terminationIndex)
+    with pytest.raises(RuntimeError, match="color must have 6 entries at dimension 2, but has 5 entries"):
+        pyr.Renderer.render_forward(inp, bad)
+    # wrong dtypes
+    with pytest.raises(RuntimeError, match="terminationIndex must be of type"):
+        pyr.Renderer.render_forward(inp, pyr.RendererOutputs(good.color, good.color[..., 0]))
+    dbl = inp.clone()
+    dbl.tf = inp.tf.double()
+    with pytest.raises(RuntimeError, match="tf must be of type"):
+        pyr.Renderer.render_forward(dbl, good)
+    # mixed devices
+    mixed = inp.clone()
+    mixed.tf = inp.tf.cpu()
+    with pytest.raises(RuntimeError, match="All tensors must be on the same device, but tf"):
+        pyr.Renderer.render_forward(mixed, good)
+    # camera variant does not match the mode (renderer.cpp:127,152,182)
+    cam = inp.clone()
+    cam.camera_mode = pyr.CameraMode.RayStartDir
+    with pytest.raises(RuntimeError, match="does not hold the first variant"):
+        pyr.Renderer.render_forward(cam, good)
+    # no adjoint variable requested (renderer.cpp:711-716)
+    pyr.Renderer.render_forward(inp, good)
+    with pytest.raises(RuntimeError, match="At least one adjoint variable must be activated"):
+        pyr.Renderer.render_adjoint(inp, good, torch.zeros_like(good.color), pyr.AdjointOutputs())
+    # forward variables cannot carry volume derivatives (renderer.cpp:541-542)
+    a = pyr.AdjointOutputs()
+    a.has_volume_derivatives = True
+    a.adj_volume = torch.zeros_like(inp.volume)
+    with pytest.raises(RuntimeError, match="volume derivatives are not supported"):
+        pyr.Renderer.forward_variables_to_gradients(torch.zeros(1, 4, 6, 1, 4, device="cuda"),
+                                                    torch.zeros(1, 4, 6, 4, device="cuda"),
+                                                    pyr.ForwardDifferencesSettings(), a)
+    # the library is still usable after the failures
+    pyr.Renderer.render_forward(inp, good)
+    pyr.sync()
+    assert torch.isfinite(good.color).all()
+
+
+def test_launches_go_to_the_current_torch_stream_and_timer_works():
+    sc = scenes.make_scene(n=24, W=64, H=48, B=2, R=8, seed=2)
+    ref_color, ref_term = pr.forward(sc)
+    inp = pr.make_inputs(sc)
+    side = torch.cuda.Stream()
+    out = pyr.RendererOutputs(torch.zeros(2, 48, 64, 4, device="cuda"), torch.zeros(2, 48, 64, dtype=torch.int32, device="cuda"))
+    torch.cuda.synchronize()
+    with torch.cuda.stream(side):
+        pyr.Renderer.render_forward(inp, out)
+        done = torch.cuda.Event()
+        done.record(side)          # ordered after the launch only if the launch went to `side`
+    done.synchronize()
+    assert np.array_equal(out.color.cpu().numpy(), ref_color) and np.array_equal(out.terminationIndex.cpu().numpy(), ref_term)
+    t = pyr.GpuTimer()
+    t.start()
+    pyr.Renderer.render_forward(inp, out)
+    t.stop()
+    assert 0.0 < t.elapsed_ms() < 1000.0

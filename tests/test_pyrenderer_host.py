@@ -1,0 +1,120 @@
+"""CPU: the C++ host layer + pybind11 module `pyrenderer` load without a GPU, expose the renderer
+surface of the reference's module (bindings/bindings.cpp:143-232, 306-511, 554-558) and reject what
+the product does not do (CPU tensors: there is no CPU back-end). No compute calls here."""
+import numpy as np
+import pytest
+import torch
+
+import pyr_runner
+import scenes
+from diffdvr_b200 import capi, load_pyrenderer
+
+pyr = load_pyrenderer()
+
+
+def test_module_surface_matches_the_reference_bindings():
+    # names as registered by the reference's PYBIND11_MODULE for the renderer path
+    functions = ["use_double_precision", "reload_kernels", "set_cuda_cache_dir", "disable_cuda_cache",
+                 "set_cuda_sync_mode", "set_cuda_debug_mode", "set_kernel_cache_file", "cleanup", "sync"]
+    classes = {"real3": ["x", "y", "z"], "real4": ["x", "y", "z", "w"], "int2": ["x", "y"], "int3": ["x", "y", "z"],
+               "CameraPerPixelRays": ["ray_start", "ray_dir"], "CameraReferenceFrame": ["viewport", "fov_y_radians"],
+               "mat4": ["to_torch"],
+               "RendererInputs": ["clone", "screen_size", "volume", "volume_filter_mode", "box_min", "box_size",
+                                  "camera_mode", "camera", "step_size", "tf_mode", "tf", "blend_mode",
+                                  "blending_early_out"],
+               "RendererOutputs": ["color", "terminationIndex"],
+               "ForwardDifferencesSettings": ["D", "d_stepsize", "d_rayStart", "d_rayDir", "d_tf", "has_tf_derivatives"],
+               "AdjointOutputs": ["has_volume_derivatives", "adj_volume", "has_stepsize_derivatives", "adj_stepsize",
+                                  "has_camera_derivatives", "adj_camera_ray_start", "adj_camera_ray_dir",
+                                  "has_tf_derivatives", "tf_delayed_accumulation", "adj_tf"],
+               "Renderer": ["render_forward", "render_forward_gradients", "render_adjoint",
+                            "forward_variables_to_gradients"],
+               "GpuTimer": ["start", "stop", "elapsed_ms"]}
+    for f in functions:
+        assert callable(getattr(pyr, f)), f
+    for c, attrs in classes.items():
+        for a in attrs:
+            assert hasattr(getattr(pyr, c), a), (c, a)
+    assert pyr.use_double_precision() == 0
+
+
+def test_enum_names_and_numeric_values():
+    # renderer/renderer_settings.cuh:81-146
+    want = {"VolumeFilterMode": dict(Nearest=0, Trilinear=1, Preshaded=3),
+            "CameraMode": dict(RayStartDir=0, InverseViewMatrix=1, ReferenceFrame=2),
+            "TFMode": dict(Identity=0, Texture=1, Linear=2, Gaussian=3, Preshaded=5, GaussianLog=6),
+            "BlendMode": dict(BeerLambert=0, Alpha=1)}
+    for enum, values in want.items():
+        for name, v in values.items():
+            assert int(getattr(getattr(pyr, enum), name)) == v
+
+
+def test_variant_fields_accept_scalars_and_tensors():
+    i = pyr.RendererInputs()
+    assert abs(i.blending_early_out - (1 - 1e-5)) < 1e-7          # renderer.h:63
+    i.box_min = pyr.real3(1, 2, 3)
+    assert (i.box_min.x, i.box_min.y, i.box_min.z) == (1, 2, 3)
+    i.box_min = torch.zeros(2, 3)
+    assert tuple(i.box_min.shape) == (2, 3)
+    i.step_size = 0.25
+    assert i.step_size == 0.25
+    i.step_size = torch.ones(1, 1, 1)
+    assert isinstance(i.step_size, torch.Tensor)
+    i.camera = pyr.CameraReferenceFrame(torch.eye(3)[None], 0.5)
+    assert i.camera.fov_y_radians == 0.5
+    i.camera = pyr.CameraPerPixelRays(torch.zeros(1, 2, 2, 3), torch.ones(1, 2, 2, 3))
+    assert float(i.camera.ray_dir.sum()) == 12
+    j = i.clone()
+    j.step_size = 1.0
+    assert isinstance(i.step_size, torch.Tensor)
+    s = pyr.ForwardDifferencesSettings()
+    assert s.d_stepsize == -1 and (s.d_rayStart.x, s.d_rayDir.z) == (-1, -1) and not s.has_tf_derivatives
+
+
+def test_mat4_buffer_round_trip():
+    a = np.arange(16, dtype=np.float32).reshape(4, 4)
+    m = pyr.mat4(a)
+    assert np.array_equal(np.array(m, copy=False), a)
+    assert torch.equal(m.to_torch(), torch.from_numpy(a)[None])
+    with pytest.raises(RuntimeError):
+        pyr.mat4(np.zeros((3, 4), np.float32))
+    with pytest.raises(RuntimeError):
+        pyr.mat4(np.zeros((4, 4), np.float64))
+
+
+def test_cpu_tensors_are_rejected_there_is_no_cpu_backend():
+    sc = scenes.make_scene(n=8, W=4, H=4, R=4)
+    inp = pyr_runner.make_inputs(sc, device="cpu")
+    out = pyr.RendererOutputs(torch.zeros(1, 4, 4, 4), torch.zeros(1, 4, 4, dtype=torch.int32))
+    with pytest.raises(RuntimeError, match="no CPU back-end"):
+        pyr.Renderer.render_forward(inp, out)
+    a = pyr.AdjointOutputs()
+    a.has_tf_derivatives = True
+    a.adj_tf = torch.zeros(1, 4, 4)
+    with pytest.raises(RuntimeError, match="no CPU back-end"):
+        pyr.Renderer.render_adjoint(inp, out, torch.zeros(1, 4, 4, 4), a)
+    with pytest.raises(RuntimeError, match="no CPU back-end"):
+        pyr.Renderer.forward_variables_to_gradients(torch.zeros(1, 4, 4, 2, 4), torch.zeros(1, 4, 4, 4),
+                                                    pyr.ForwardDifferencesSettings(), a)
+    u = pyr.RendererInputs()
+    with pytest.raises(RuntimeError, match="volume is not defined"):
+        pyr.Renderer.render_forward(u, out)
+
+
+def test_options_and_control_shims():
+    assert pyr.get_option("compat_stepsize_overwrite") == 0
+    pyr.set_option("compat_stepsize_overwrite", 1)
+    assert capi.load().get_option("compat_stepsize_overwrite") == 1   # one library behind both front ends
+    pyr.set_option("compat_stepsize_overwrite", 0)
+    with pytest.raises(RuntimeError):
+        pyr.set_option("no_such_option", 1)
+    pyr.set_cuda_sync_mode(True)
+    assert pyr.get_cuda_sync_mode()
+    pyr.set_cuda_sync_mode(False)
+    for f in (pyr.reload_kernels, pyr.disable_cuda_cache, pyr.cleanup):
+        f()
+    pyr.set_cuda_cache_dir("/tmp/x")
+    pyr.set_kernel_cache_file("k")
+    pyr.set_cuda_debug_mode(False)
+    assert pyr.has_variant(pyr.VolumeFilterMode.Trilinear, pyr.CameraMode.ReferenceFrame, pyr.TFMode.Texture,
+                           pyr.BlendMode.BeerLambert)
