@@ -411,6 +411,7 @@ int dvr_render_adjoint(const DvrInputs* inputs, const DvrOutputs* fwd, const Dvr
     const bool hasRay = aa.hasStep || aa.hasCam;
     if (!hasVol && !hasTf && !hasRay) fail(DVR_ERR_INVALID_ARGUMENT, "At least one adjoint variable must be activated!");
     aa.compatStepOverwrite = g_compat_stepsize.load();
+    aa.sameStrides = hasVol && aa.avx == c.ri.sx && aa.avy == c.ri.sy && aa.avz == c.ri.sz;
     const int tf = inputs->tf_mode;
     int tfacc = kTfAccNone;
     if (hasTf) tfacc = (tf == kTfIdentity || c.ri.R <= kRegRows) ? kTfAccReg : kTfAccSmem;

@@ -317,7 +317,7 @@ __global__ void __launch_bounds__(kThreads) k_adjoint(const RayInputs in, const 
         adjStep = fmaf(adjT, fi, adjStep);
       }
     }
-    smp.flush();
+    smp.flush(&aa);
     if constexpr (HAS_RAY) {
       if (aa.hasStep) {
         float* p = aa.adjStep + b * aa.asB + y * aa.asY + x * aa.asX;

@@ -63,6 +63,7 @@ struct AdjointArgs {
   float* adjVolume;                  // element offsets like the volume
   long long avB;
   int avx, avy, avz;
+  int sameStrides;                   // adj_volume has the element strides of the volume
   float* adjStep;
   long long asB, asY, asX;
   int stepAtomic;                    // broadcasting -> atomics (renderer_kernels.cuh:418-421)

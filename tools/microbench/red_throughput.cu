@@ -5,6 +5,7 @@
 //   mode 2: 4 x red.global.v4.f32.add, aligned quad containing z0,z0+1, zero padded
 //   mode 3: mixed: v2 when z0 even else 2 scalar (what a real kernel can do with v2 only)
 //   mode 4: mixed: v4 zero padded when (z0&3)!=3 else 2 scalar
+//   mode 5: mixed: v2 when z0 even, v4 {0,a,b,0} when z0%4==1, scalar when z0%4==3
 // Each lane walks a ray-like sequence of cells: warp lanes sit in an 8x4 patch (0.6 voxel pitch)
 // and advance along a direction; every iteration flushes one cell (8 corners).
 // build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o red_throughput red_throughput.cu
@@ -53,6 +54,17 @@ __global__ void __launch_bounds__(128) k(float* vol, int n, int iters, float pit
         red1(c, a); red1(c + 1, a); red1(c + sy, a); red1(c + sy + 1, a);
         red1(c + sx, a); red1(c + sx + 1, a); red1(c + sx + sy, a); red1(c + sx + sy + 1, a);
       }
+    } else if (MODE == 5) {
+      const int q = z0 & 3;
+      if ((q & 1) == 0) {
+        red2(c, a, a); red2(c + sy, a, a); red2(c + sx, a, a); red2(c + sx + sy, a, a);
+      } else if (q == 1) {
+        float* e = c - 1;
+        red4(e, 0.f, a, a, 0.f); red4(e + sy, 0.f, a, a, 0.f); red4(e + sx, 0.f, a, a, 0.f); red4(e + sx + sy, 0.f, a, a, 0.f);
+      } else {
+        red1(c, a); red1(c + 1, a); red1(c + sy, a); red1(c + sy + 1, a);
+        red1(c + sx, a); red1(c + sx + 1, a); red1(c + sx + sy, a); red1(c + sx + sy + 1, a);
+      }
     } else {
       const int q = z0 & 3;
       if (q != 3) {
@@ -91,7 +103,7 @@ int main() {
   float* vol;
   cudaMalloc(&vol, sizeof(float) * n * n * n);
   cudaMemset(vol, 0, sizeof(float) * n * n * n);
-  run<0>(vol, n, iters); run<1>(vol, n, iters); run<2>(vol, n, iters); run<3>(vol, n, iters); run<4>(vol, n, iters);
+  run<0>(vol, n, iters); run<1>(vol, n, iters); run<2>(vol, n, iters); run<3>(vol, n, iters); run<4>(vol, n, iters); run<5>(vol, n, iters);
   cudaError_t e = cudaDeviceSynchronize();
   printf("status: %s\n", cudaGetErrorString(e));
   return e != cudaSuccess;
