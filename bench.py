@@ -384,10 +384,17 @@ def run_ours(a):
 
 def main():
     a = parse_args()
+    # the contract is ONE JSON line on stdout: libraries (NCCL prints its version banner there) get
+    # stderr as their stdout for the whole run, the JSON line goes to the real stdout at the end
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real_stdout
     if a.impl == "reference":
         run_reference(a)
     else:
         run_ours(a)
+    real_stdout.flush()
 
 
 if __name__ == "__main__":

@@ -99,10 +99,16 @@ void check_inputs(const DvrInputs& a, Checked& c) {
   const bool preshaded = a.volume_filter_mode == DVR_FILTER_PRESHADED;
   if (preshaded != (a.tf_mode == DVR_TF_PRESHADED))
     fail(DVR_ERR_INVALID_ARGUMENT, "if pre-shading is selected, both the filter mode and TF mode must be set to preshaded");
-  if (preshaded) fail(DVR_ERR_UNSUPPORTED, "pre-shaded volumes (FilterPreshaded/TFPreshaded) have no sm_100a instance yet");
-  if (a.volume_filter_mode != DVR_FILTER_NEAREST && a.volume_filter_mode != DVR_FILTER_TRILINEAR)
+  if (a.volume_filter_mode != DVR_FILTER_NEAREST && a.volume_filter_mode != DVR_FILTER_TRILINEAR && !preshaded)
     fail(DVR_ERR_UNSUPPORTED, "volume filter mode %d is not supported", a.volume_filter_mode);
   int B = int(a.volume.size[0]);
+  if (preshaded) {  // renderer.cpp:78-83: the four colour channels sit in the batch dimension
+    if (a.volume.size[0] != 4)
+      fail(DVR_ERR_INVALID_ARGUMENT,
+           "In pre-shaded mode, the volume colors are encoded in the batch dimension of the volume. It must be 4, but is %lld",
+           (long long)a.volume.size[0]);
+    B = 1;
+  }
   c.X = int(a.volume.size[1]);
   c.Y = int(a.volume.size[2]);
   c.Z = int(a.volume.size[3]);
@@ -114,7 +120,7 @@ void check_inputs(const DvrInputs& a, Checked& c) {
       fail(DVR_ERR_UNSUPPORTED, "one volume batch entry must span fewer than 2^31 elements");
   }
   r.volume = static_cast<const float*>(a.volume.ptr);
-  r.volB = bstride(a.volume, 0);
+  r.volB = preshaded ? a.volume.stride[0] : bstride(a.volume, 0);
   r.sx = int(bstride(a.volume, 1));
   r.sy = int(bstride(a.volume, 2));
   r.sz = int(bstride(a.volume, 3));
@@ -206,9 +212,10 @@ void check_inputs(const DvrInputs& a, Checked& c) {
       break;
     case DVR_TF_GAUSSIAN:
     case DVR_TF_GAUSSIAN_LOG: check_size(a.tf, "tf", 2, 6); break;
+    case DVR_TF_PRESHADED: break;  // any size is allowed, the TF is ignored (renderer.cpp:240-242)
     default: fail(DVR_ERR_INVALID_ARGUMENT, "unknown tf enum value");
   }
-  if (a.tf.size[1] < 1) fail(DVR_ERR_INVALID_ARGUMENT, "tensor 'tf' must have at least one row");
+  if (a.tf.size[1] < 1 && !preshaded) fail(DVR_ERR_INVALID_ARGUMENT, "tensor 'tf' must have at least one row");
   r.tf = {static_cast<const float*>(a.tf.ptr), bstride(a.tf, 0), a.tf.stride[1], a.tf.stride[2]};
   r.R = int(a.tf.size[1]);
   r.C = int(a.tf.size[2]);
@@ -255,10 +262,11 @@ size_t check_smem(size_t bytes) {
 
 // checkAdjointOutput (renderer/renderer.cpp:265-365); X<0 skips the volume checks
 void check_adjoint_outputs(const DvrAdjointOutputs& o, int B, int H, int W, int X, int Y, int Z, const DvrTensor* tf,
-                           AdjointArgs& aa) {
+                           AdjointArgs& aa, bool preshaded = false) {
   if (o.has_volume_derivatives) {
     check_dim(o.adj_volume, "adj_volume", 4);
-    check_batch(o.adj_volume, "adj_volume", B);
+    if (preshaded) check_size(o.adj_volume, "adj_volume", 0, 4);  // renderer.cpp:277-279
+    else check_batch(o.adj_volume, "adj_volume", B);
     check_size(o.adj_volume, "adj_volume", 1, X);
     check_size(o.adj_volume, "adj_volume", 2, Y);
     check_size(o.adj_volume, "adj_volume", 3, Z);
@@ -266,7 +274,7 @@ void check_adjoint_outputs(const DvrAdjointOutputs& o, int B, int H, int W, int 
     for (int d = 1; d < 4; ++d) span += (o.adj_volume.size[d] - 1) * bstride(o.adj_volume, d);
     if (span >= (1ll << 31)) fail(DVR_ERR_UNSUPPORTED, "one adj_volume batch entry must span fewer than 2^31 elements");
     aa.adjVolume = static_cast<float*>(o.adj_volume.ptr);
-    aa.avB = bstride(o.adj_volume, 0);
+    aa.avB = preshaded ? o.adj_volume.stride[0] : bstride(o.adj_volume, 0);
     aa.avx = int(bstride(o.adj_volume, 1));
     aa.avy = int(bstride(o.adj_volume, 2));
     aa.avz = int(bstride(o.adj_volume, 3));
@@ -301,7 +309,7 @@ void check_adjoint_outputs(const DvrAdjointOutputs& o, int B, int H, int W, int 
   if (o.has_tf_derivatives) {
     check_dim(o.adj_tf, "adj_tf", 3);
     check_batch(o.adj_tf, "adj_tf", B);
-    if (tf) {
+    if (tf && !preshaded) {
       check_size(o.adj_tf, "adj_tf", 1, tf->size[1]);
       check_size(o.adj_tf, "adj_tf", 2, tf->size[2]);
     }
@@ -370,8 +378,12 @@ int dvr_render_forward(const DvrInputs* inputs, const DvrOutputs* outputs, void*
     Checked c;
     check_inputs(*inputs, c);
     const ForwardOutputs fo = check_outputs(*outputs, c);
-    const size_t smem = check_smem(size_t(c.ri.R) * tf_row(inputs->tf_mode) * sizeof(float));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (inputs->tf_mode == DVR_TF_PRESHADED) {
+      after_launch(launch_forward_preshaded(inputs->blend_mode, c.ri, fo, tile_grid(c), s), "dvr_render_forward", s);
+      return;
+    }
+    const size_t smem = check_smem(size_t(c.ri.R) * tf_row(inputs->tf_mode) * sizeof(float));
     after_launch(launch_forward(inputs->volume_filter_mode, inputs->tf_mode, inputs->blend_mode, c.ri, fo,
                                 tile_grid(c), smem, s),
                  "dvr_render_forward", s);
@@ -406,12 +418,21 @@ int dvr_render_adjoint(const DvrInputs* inputs, const DvrOutputs* fwd, const Dvr
     aa.tB = bstride(fwd->termination_index, 0);
     aa.tY = bstride(fwd->termination_index, 1);
     aa.tX = bstride(fwd->termination_index, 2);
-    check_adjoint_outputs(*adj, c.B, c.H, c.W, c.X, c.Y, c.Z, &inputs->tf, aa);
+    const bool preshaded = inputs->tf_mode == DVR_TF_PRESHADED;
+    check_adjoint_outputs(*adj, c.B, c.H, c.W, c.X, c.Y, c.Z, &inputs->tf, aa, preshaded);
     const bool hasVol = adj->has_volume_derivatives != 0, hasTf = adj->has_tf_derivatives != 0;
     const bool hasRay = aa.hasStep || aa.hasCam;
     if (!hasVol && !hasTf && !hasRay) fail(DVR_ERR_INVALID_ARGUMENT, "At least one adjoint variable must be activated!");
     aa.compatStepOverwrite = g_compat_stepsize.load();
     aa.sameStrides = hasVol && aa.avx == c.ri.sx && aa.avy == c.ri.sy && aa.avz == c.ri.sz;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (preshaded) {
+      // the pre-shaded TF has no parameters: a request for adj_tf alone is valid and a no-op
+      if (hasVol || hasRay)
+        after_launch(launch_adjoint_preshaded(inputs->blend_mode, hasVol, hasRay, c.ri, aa, tile_grid(c), s),
+                     "dvr_render_adjoint", s);
+      return;
+    }
     const int tf = inputs->tf_mode;
     int tfacc = kTfAccNone;
     if (hasTf) tfacc = (tf == kTfIdentity || c.ri.R <= kRegRows) ? kTfAccReg : kTfAccSmem;
@@ -419,7 +440,6 @@ int dvr_render_adjoint(const DvrInputs* inputs, const DvrOutputs* fwd, const Dvr
     const int ntab = tfacc == kTfAccSmem ? kThreads / 32 : (tfacc == kTfAccReg ? 1 : 0);
     const size_t smem =
         check_smem((size_t((c.ri.R * tf_row(tf) + 3) & ~3) + size_t(ntab) * entries) * sizeof(float));
-    cudaStream_t s = static_cast<cudaStream_t>(stream);
     after_launch(launch_adjoint(inputs->volume_filter_mode, tf, inputs->blend_mode, hasVol, tfacc, hasRay, c.ri, aa,
                                 tile_grid(c), smem, s),
                  "dvr_render_adjoint", s);
@@ -438,6 +458,8 @@ int dvr_render_forward_gradients(const DvrInputs* inputs, const DvrForwardDiffer
     for (int i = 0; i < 3; ++i) hasCam = hasCam || st->d_ray_start[i] >= 0 || st->d_ray_dir[i] >= 0;
     const bool hasTf = st->has_tf_derivatives != 0;
     if (!hasStep && !hasCam && !hasTf) fail(DVR_ERR_INVALID_ARGUMENT, "at least one derivative must be activated");
+    if (inputs->tf_mode == DVR_TF_PRESHADED)
+      fail(DVR_ERR_UNSUPPORTED, "forward derivatives are not available for pre-shaded volumes");
     if (inputs->tf_mode == DVR_TF_GAUSSIAN_LOG)
       fail(DVR_ERR_UNSUPPORTED, "forward derivatives are not supported for TFGaussianLog (deleted in the reference, renderer_tf.cuh:692-702)");
     ForwardGradArgs ga;
@@ -557,8 +579,11 @@ int dvr_count_cell_visits(const DvrInputs* inputs, const DvrTensor* termination_
 }
 
 int dvr_has_variant(int32_t filter, int32_t camera, int32_t tf, int32_t blend) {
-  const bool f = filter == DVR_FILTER_NEAREST || filter == DVR_FILTER_TRILINEAR;
   const bool c = camera >= 0 && camera <= 2;
+  if (filter == DVR_FILTER_PRESHADED || tf == DVR_TF_PRESHADED)  // only valid together
+    return filter == DVR_FILTER_PRESHADED && tf == DVR_TF_PRESHADED && c &&
+           (blend == DVR_BLEND_BEER_LAMBERT || blend == DVR_BLEND_ALPHA);
+  const bool f = filter == DVR_FILTER_NEAREST || filter == DVR_FILTER_TRILINEAR;
   const bool t = tf == DVR_TF_IDENTITY || tf == DVR_TF_TEXTURE || tf == DVR_TF_LINEAR || tf == DVR_TF_GAUSSIAN ||
                  tf == DVR_TF_GAUSSIAN_LOG;
   const bool b = blend == DVR_BLEND_BEER_LAMBERT || blend == DVR_BLEND_ALPHA;

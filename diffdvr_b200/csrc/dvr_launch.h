@@ -23,6 +23,12 @@ cudaError_t launch_forward_gradients(int filter, int tf, int blend, int chunk, b
                                      const ForwardGradArgs& ga, dim3 grid, size_t smem,
                                      cudaStream_t stream);
 
+// pre-shaded volumes (FilterPreshaded + TFPreshaded), dvr_preshaded.cu
+cudaError_t launch_forward_preshaded(int blend, const RayInputs& in, const ForwardOutputs& out, dim3 grid,
+                                     cudaStream_t stream);
+cudaError_t launch_adjoint_preshaded(int blend, bool hasVol, bool hasRay, const RayInputs& in,
+                                     const AdjointArgs& aa, dim3 grid, cudaStream_t stream);
+
 cudaError_t launch_fwdvars_to_gradients(const FwdVarsArgs& a, cudaStream_t stream);
 
 cudaError_t launch_count_cells(const RayInputs& in, const int* term, long long tB, long long tY, long long tX,

@@ -37,6 +37,11 @@ def cases():
         ("tri_xfast_randvol_texture", mk(n=12, W=11, H=9, B=2, camera_mode=C, tf_mode=T, R=4, seed=27, opacity=4.0,
                                          volume_kind="rand", x_fastest=True, tensor_scalars=True),
          all_flags, "tf"),
+        ("pre_frame_beer", mk(n=12, W=12, H=10, B=2, camera_mode=C, filter_mode=capi.FILTER_PRESHADED, seed=28,
+                              opacity=4.0), dict(volume=True, step=True, camera=True, tf=False), None),
+        ("pre_rays_alpha", mk(n=12, W=11, H=9, B=1, camera_mode=capi.CAMERA_RAY_START_DIR,
+                              filter_mode=capi.FILTER_PRESHADED, blend_mode=capi.BLEND_ALPHA, seed=29, opacity=4.0),
+         dict(volume=True, step=True, camera=True, tf=False), None),
         ("consistency_tf_texture8", scenes.consistency_tf_scene(T, 8, seed=8, W=24, H=24),
          dict(volume=False, step=False, camera=False, tf=True), "tf"),
         ("consistency_camera_linear4", scenes.consistency_camera_scene(capi.TF_LINEAR, 4, seed=4),

@@ -68,6 +68,11 @@ def test_has_variant_covers_the_reference_instantiation_set():
             for t in (capi.TF_IDENTITY, capi.TF_TEXTURE, capi.TF_LINEAR, capi.TF_GAUSSIAN, capi.TF_GAUSSIAN_LOG):
                 for b in (0, 1):
                     assert lib.has_variant(f, c, t, b)
+    for c in (0, 1, 2):   # pre-shaded volumes: filter and TF only together
+        for b in (0, 1):
+            assert lib.has_variant(capi.FILTER_PRESHADED, c, capi.TF_PRESHADED, b)
+    assert not lib.has_variant(capi.FILTER_PRESHADED, 0, capi.TF_TEXTURE, 0)
+    assert not lib.has_variant(capi.FILTER_TRILINEAR, 0, capi.TF_PRESHADED, 0)
     assert not lib.has_variant(capi.FILTER_NETWORK, 0, capi.TF_TEXTURE, 0)
     assert not lib.has_variant(capi.FILTER_TRILINEAR, 7, capi.TF_TEXTURE, 0)
 

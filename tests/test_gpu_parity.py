@@ -178,3 +178,22 @@ def test_error_paths_return_codes_not_crashes():
     with pytest.raises(capi.DvrError) as e:  # no adjoint variable activated
         lib.render_adjoint(inp, color, term, color, capi.make_adjoint_outputs())
     assert "At least one adjoint variable" in str(e.value)
+
+
+@pytest.mark.parametrize("cam", [capi.CAMERA_RAY_START_DIR, capi.CAMERA_INVERSE_VIEW_MATRIX, capi.CAMERA_REFERENCE_FRAME])
+@pytest.mark.parametrize("blend", [capi.BLEND_BEER_LAMBERT, capi.BLEND_ALPHA])
+def test_preshaded_volumes(oracles, cam, blend):
+    """FilterPreshaded + TFPreshaded (renderer_interpolation.cuh:393-579, renderer_tf.cuh:819-854): RGBA in the
+    batch dimension of the volume, 4-channel gradient, including the reference's position-adjoint typo."""
+    sc = scenes.make_scene(n=14, W=18, H=14, B=2, camera_mode=cam, blend_mode=blend, filter_mode=capi.FILTER_PRESHADED,
+                           seed=31, opacity=5.0)
+    run_case(oracles, sc, volume=True, step=True, camera=True, tf=False)
+    # adj_tf alone is accepted and a no-op (the pre-shaded TF has no parameters)
+    color, term = gr.forward(sc)
+    out = gr.adjoint(sc, color, term, np.ones_like(color), tf=True)
+    assert not out["adj_tf"].any()
+    # wrong channel count
+    bad = scenes.make_scene(n=8, W=4, H=4, filter_mode=capi.FILTER_PRESHADED)
+    bad.volume = bad.volume[:3]
+    with pytest.raises(capi.DvrError, match="must be 4, but is 3"):
+        gr.forward(bad)
