@@ -330,6 +330,43 @@ void fill_fd_settings(const DvrForwardDifferencesSettings& s, int* dStep, int* d
   }
 }
 
+// shared by dvr_generate_rays / dvr_generate_rays_adjoint: GenerateRayFunction::forward checks
+// (renderer/camera.cpp:189-193) and the shapes of the two B*H*W*3 ray tensors
+void fill_gen_rays(const DvrTensor& viewport, float fovY, int W, int H, const DvrTensor& start, const DvrTensor& dir,
+                   const char* nameStart, const char* nameDir, GenRaysArgs& a) {
+  std::memset(&a, 0, sizeof(a));
+  check_dim(viewport, "viewport", 3);
+  check_size(viewport, "viewport", 1, 3);
+  check_size(viewport, "viewport", 2, 3);
+  const int B = int(viewport.size[0]);
+  if (W <= 0 || H <= 0) fail(DVR_ERR_INVALID_ARGUMENT, "screen size must be positive, but is (%d, %d)", W, H);
+  if (B < 1 || B > 65535) fail(DVR_ERR_UNSUPPORTED, "batch size %d outside [1, 65535]", B);
+  const DvrTensor* ts[2] = {&start, &dir};
+  const char* names[2] = {nameStart, nameDir};
+  for (int k = 0; k < 2; ++k) {
+    check_dim(*ts[k], names[k], 4);
+    check_size(*ts[k], names[k], 0, B);
+    check_size(*ts[k], names[k], 1, H);
+    check_size(*ts[k], names[k], 2, W);
+    check_size(*ts[k], names[k], 3, 3);
+  }
+  a.W = W; a.H = H; a.B = B;
+  a.viewport = {static_cast<const float*>(viewport.ptr), viewport.stride[0], viewport.stride[1], viewport.stride[2]};
+  // camera_impl.cu:76-78
+  const float fovX = fovY * float(W) / float(H);
+  a.tanFovX = tanf(fovX / 2);
+  a.tanFovY = tanf(fovY / 2);
+  a.rayStart = static_cast<float*>(start.ptr);
+  a.sB = start.stride[0]; a.sY = start.stride[1]; a.sX = start.stride[2]; a.sC = start.stride[3];
+  a.rayDir = static_cast<float*>(dir.ptr);
+  a.dB = dir.stride[0]; a.dY = dir.stride[1]; a.dX = dir.stride[2]; a.dC = dir.stride[3];
+  auto packed = [&](const DvrTensor& t) {
+    return t.stride[3] == 1 && t.stride[2] == 3 && t.stride[1] == 3ll * W && t.stride[0] == 3ll * W * H &&
+           reinterpret_cast<uintptr_t>(t.ptr) % 16 == 0;
+  };
+  a.packed = W % 4 == 0 && packed(start) && packed(dir);
+}
+
 }  // namespace
 
 namespace dvr {
@@ -556,6 +593,98 @@ int dvr_forward_variables_to_gradients(const DvrTensor* fv, const DvrTensor* gc,
     check_smem(size_t(a.R) * a.C * sizeof(float));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     after_launch(launch_fwdvars_to_gradients(a, s), "dvr_forward_variables_to_gradients", s);
+  });
+}
+
+int dvr_generate_rays(const DvrTensor* viewport, float fov_y, int32_t W, int32_t H, const DvrTensor* ray_start,
+                      const DvrTensor* ray_dir, void* stream) {
+  return guarded([&] {
+    if (!viewport || !ray_start || !ray_dir) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    GenRaysArgs a;
+    fill_gen_rays(*viewport, fov_y, W, H, *ray_start, *ray_dir, "rayStart", "rayDir", a);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    after_launch(launch_generate_rays(a, s), "dvr_generate_rays", s);
+  });
+}
+
+int dvr_generate_rays_adjoint(const DvrTensor* viewport, float fov_y, const DvrTensor* adj_ray_start,
+                              const DvrTensor* adj_ray_dir, const DvrTensor* adj_viewport, void* stream) {
+  return guarded([&] {
+    if (!viewport || !adj_ray_start || !adj_ray_dir || !adj_viewport) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    check_dim(*adj_ray_start, "adj_rayStart", 4);
+    GenRaysArgs a;
+    fill_gen_rays(*viewport, fov_y, int(adj_ray_start->size[2]), int(adj_ray_start->size[1]), *adj_ray_start,
+                  *adj_ray_dir, "adj_rayStart", "adj_rayDir", a);
+    check_dim(*adj_viewport, "adj_viewport", 3);
+    check_size(*adj_viewport, "adj_viewport", 0, a.B);
+    check_size(*adj_viewport, "adj_viewport", 1, 3);
+    check_size(*adj_viewport, "adj_viewport", 2, 3);
+    a.adjViewport = static_cast<float*>(adj_viewport->ptr);
+    a.avB = adj_viewport->stride[0]; a.avR = adj_viewport->stride[1]; a.avC = adj_viewport->stride[2];
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    cuda_check(launch_generate_rays_adjoint(a, s), "dvr_generate_rays_adjoint");
+    g_launches.fetch_add(1, std::memory_order_relaxed);  // zero + reduce = 2 launches
+    after_launch(cudaSuccess, "dvr_generate_rays_adjoint", s);
+  });
+}
+
+int dvr_compare_to_image(const DvrTensor* color, const DvrTensor* grads, const DvrTensor* reference,
+                         const DvrTensor* diff_out, const DvrTensor* grads_out, int32_t reduce, void* stream) {
+  return guarded([&] {
+    if (!color || !grads || !reference || !diff_out || !grads_out) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    // Renderer::compareToImage (renderer/renderer.cpp:566-593)
+    check_dim(*color, "colorInput", 4);
+    const int B = int(color->size[0]), H = int(color->size[1]), W = int(color->size[2]);
+    check_size(*color, "colorInput", 3, 4);
+    check_dim(*grads, "gradientsInput", 5);
+    check_size(*grads, "gradientsInput", 0, B);
+    check_size(*grads, "gradientsInput", 1, H);
+    check_size(*grads, "gradientsInput", 2, W);
+    const int D = int(grads->size[3]);
+    check_size(*grads, "gradientsInput", 4, 4);
+    check_dim(*reference, "colorReference", 4);
+    check_size(*reference, "colorReference", 0, B);
+    check_size(*reference, "colorReference", 1, H);
+    check_size(*reference, "colorReference", 2, W);
+    check_size(*reference, "colorReference", 3, 4);
+    CompareArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.W = W; a.H = H; a.B = B; a.D = D;
+    a.color = {static_cast<const float*>(color->ptr), color->stride[0], color->stride[1], color->stride[2], color->stride[3]};
+    a.reference = {static_cast<const float*>(reference->ptr), reference->stride[0], reference->stride[1],
+                   reference->stride[2], reference->stride[3]};
+    a.grad = static_cast<const float*>(grads->ptr);
+    a.gB = grads->stride[0]; a.gY = grads->stride[1]; a.gX = grads->stride[2]; a.gD = grads->stride[3]; a.gC = grads->stride[4];
+    a.reduce = reduce != 0;
+    a.diffOut = static_cast<float*>(diff_out->ptr);
+    a.gradOut = static_cast<float*>(grads_out->ptr);
+    if (a.reduce) {  // renderer.cpp:598-608
+      check_dim(*diff_out, "differenceOut", 1);
+      check_size(*diff_out, "differenceOut", 0, 1);
+      check_dim(*grads_out, "gradientsOut", 1);
+      check_size(*grads_out, "gradientsOut", 0, D);
+      a.qD = grads_out->stride[0];
+      a.normalization = 1.0f / float((long long)B * H * W);
+      if (D > 8192) fail(DVR_ERR_UNSUPPORTED, "more than 8192 derivatives in the reduced comparison");
+    } else {  // renderer.cpp:625-641
+      check_dim(*diff_out, "differenceOut", 4);
+      check_size(*diff_out, "differenceOut", 0, B);
+      check_size(*diff_out, "differenceOut", 1, H);
+      check_size(*diff_out, "differenceOut", 2, W);
+      check_size(*diff_out, "differenceOut", 3, 1);
+      check_dim(*grads_out, "gradientsOut", 4);
+      check_size(*grads_out, "gradientsOut", 0, B);
+      check_size(*grads_out, "gradientsOut", 1, H);
+      check_size(*grads_out, "gradientsOut", 2, W);
+      check_size(*grads_out, "gradientsOut", 3, D);
+      a.oB = diff_out->stride[0]; a.oY = diff_out->stride[1]; a.oX = diff_out->stride[2];
+      a.qB = grads_out->stride[0]; a.qY = grads_out->stride[1]; a.qX = grads_out->stride[2]; a.qD = grads_out->stride[3];
+    }
+    if ((long long)B * H * W == 0) return;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    cuda_check(launch_compare_to_image(a, s), "dvr_compare_to_image");
+    if (a.reduce) g_launches.fetch_add(1, std::memory_order_relaxed);  // zero + reduce
+    after_launch(cudaSuccess, "dvr_compare_to_image", s);
   });
 }
 

@@ -34,6 +34,11 @@ cudaError_t launch_fwdvars_to_gradients(const FwdVarsArgs& a, cudaStream_t strea
 cudaError_t launch_count_cells(const RayInputs& in, const int* term, long long tB, long long tY, long long tX,
                                unsigned long long* counts, dim3 grid, cudaStream_t stream);
 
+// Camera::generateRays forward / adjoint and Renderer::compareToImage (dvr_camera.cu)
+cudaError_t launch_generate_rays(const GenRaysArgs& a, cudaStream_t stream);
+cudaError_t launch_generate_rays_adjoint(const GenRaysArgs& a, cudaStream_t stream);  // 2 launches
+cudaError_t launch_compare_to_image(const CompareArgs& a, cudaStream_t stream);       // reduce: 2 launches
+
 // per-(tf, blend) translation units (parallel compilation)
 #define DVR_DECL_ADJ(TF, BL)                                                                          \
   cudaError_t launch_adjoint_##TF##_##BL(int filter, bool hasVol, int tfacc, bool hasRay,             \

@@ -110,4 +110,32 @@ struct FwdVarsArgs {
   long long atB, atR, atC;
 };
 
+// Camera::generateRays forward / adjoint (renderer/camera_impl.cu:17-94, 96-356)
+struct GenRaysArgs {
+  int W, H, B;
+  StridedMat viewport;               // B*3*3 (eye, right, up)
+  float tanFovX, tanFovY;
+  float* rayStart;                   // B*H*W*3 (forward: written; adjoint: read)
+  long long sB, sY, sX, sC;
+  float* rayDir;
+  long long dB, dY, dX, dC;
+  int packed;                        // both ray tensors contiguous, W % 4 == 0, 16-byte aligned
+  float* adjViewport;                // adjoint: B*3*3, zeroed by the launcher, accumulated
+  long long avB, avR, avC;
+};
+
+// Renderer::compareToImage (renderer/renderer_compareToImage.cuh:9-65, renderer_cuda_impl.cu:9-172)
+struct CompareArgs {
+  int W, H, B, D;
+  Strided4 color, reference;         // B*H*W*4
+  const float* grad;                 // B*H*W*D*4
+  long long gB, gY, gX, gD, gC;
+  int reduce;
+  float normalization;               // 1 / (B*H*W), reduce only
+  float* diffOut;                    // !reduce: B*H*W*1 ; reduce: 1
+  long long oB, oY, oX;
+  float* gradOut;                    // !reduce: B*H*W*D ; reduce: D
+  long long qB, qY, qX, qD;
+};
+
 }  // namespace dvr

@@ -172,6 +172,34 @@ DVR_API int dvr_render_adjoint(const DvrInputs* inputs, const DvrOutputs* output
                        const DvrTensor* adj_color, const DvrAdjointOutputs* adj_outputs,
                        void* stream);
 
+/* ---- callers either side of the marcher ------------------------ */
+
+/* Camera::generateRays, forward (renderer/camera.cpp:182-213 -> kernel::generateRaysForward,
+ * renderer/camera_impl.cu:17-94). viewport: B*3*3 rows eye/right/up; writes ray_start and
+ * ray_dir, both B*H*W*3 (any strides; contiguous tensors with W % 4 == 0 take a 128-bit path). */
+DVR_API int dvr_generate_rays(const DvrTensor* viewport, float fov_y_radians, int32_t screen_width,
+                      int32_t screen_height, const DvrTensor* ray_start, const DvrTensor* ray_dir,
+                      void* stream);
+
+/* Camera::generateRays, backward (renderer/camera.cpp:215-246 -> kernel::generateRaysAdjoint,
+ * renderer/camera_impl.cu:96-356, a cub segmented reduction in the reference).
+ * adj_viewport (B*3*3) is OVERWRITTEN with the per-view sums, like the reference. */
+DVR_API int dvr_generate_rays_adjoint(const DvrTensor* viewport, float fov_y_radians,
+                              const DvrTensor* adj_ray_start, const DvrTensor* adj_ray_dir,
+                              const DvrTensor* adj_viewport, void* stream);
+
+/* Renderer::compareToImage (renderer/renderer.cpp:562-657 -> RendererCuda::compareToImage_*,
+ * renderer/renderer_cuda_impl.cu:112-172 over renderer/renderer_compareToImage.cuh:9-65):
+ * per-pixel L2 norm |color_input - color_reference| over RGBA and its D forward derivatives.
+ *   reduce == 0: difference_out B*H*W*1, gradients_out B*H*W*D
+ *   reduce != 0: difference_out 1, gradients_out D; the mean over all B*H*W pixels
+ * Both outputs are overwritten (the reference zeroes them first). Any D >= 0 is accepted
+ * (the reference's CUDA path prints an error and does nothing for D != 1,
+ * renderer_cuda_impl.cu:106-110). */
+DVR_API int dvr_compare_to_image(const DvrTensor* color_input, const DvrTensor* gradients_input,
+                         const DvrTensor* color_reference, const DvrTensor* difference_out,
+                         const DvrTensor* gradients_out, int32_t reduce, void* stream);
+
 /* Measurement utility (bench accounting): re-walks every ray up to its
  * terminationIndex and counts samples and CELL VISITS (a sample whose integer cell differs
  * from the ray's previous one -- the unit the reference's cell cache reloads 8 corners for,

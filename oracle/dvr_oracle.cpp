@@ -914,6 +914,10 @@ static void face_distance(const DvrInputs& in, const DvrTensor& termT, const Dvr
   }
 }
 
+}  // namespace dvro
+#include "dvr_oracle_camera.h"
+namespace dvro {
+
 template <typename F>
 static int guarded(F&& f) {
   try {
@@ -951,6 +955,20 @@ using namespace dvro;
   }                                                                                                 \
   extern "C" int dvro##P##_face_distance(const DvrInputs* i, const DvrTensor* t, const DvrTensor* o) { \
     return guarded([&] { face_distance<R>(*i, *t, *o); });                                          \
+  }                                                                                                 \
+  extern "C" int dvro##P##_generate_rays(const DvrTensor* vp, float fovY, int32_t W, int32_t H,     \
+                                         const DvrTensor* rs, const DvrTensor* rd, void*) {         \
+    return guarded([&] { generate_rays<R>(*vp, fovY, W, H, *rs, *rd); });                           \
+  }                                                                                                 \
+  extern "C" int dvro##P##_generate_rays_adjoint(const DvrTensor* vp, float fovY,                   \
+                                                 const DvrTensor* as, const DvrTensor* ad,         \
+                                                 const DvrTensor* av, void*) {                      \
+    return guarded([&] { generate_rays_adjoint<R>(*vp, fovY, *as, *ad, *av); });                    \
+  }                                                                                                 \
+  extern "C" int dvro##P##_compare_to_image(const DvrTensor* c, const DvrTensor* g,                 \
+                                            const DvrTensor* q, const DvrTensor* d,                \
+                                            const DvrTensor* go, int32_t reduce, void*) {           \
+    return guarded([&] { compare_to_image<R>(*c, *g, *q, *d, *go, reduce); });                      \
   }                                                                                                 \
   extern "C" const char* dvro##P##_last_error() { return g_error.c_str(); }                         \
   extern "C" int dvro##P##_real_size() { return int(sizeof(R)); }

@@ -24,21 +24,33 @@ __device__ __forceinline__ void red4(float* p, float a, float b, float c, float 
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(128) k(float* vol, int n, int iters, float pitch) {
+__global__ void __launch_bounds__(128) k(float* vol, int n, int iters, float pitch, int dirsel) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tx = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
   const int ty = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
   // ray through the volume, mostly along z for even blockIdx.z, along x for odd
   float px = tx * pitch, py = ty * pitch, pz = 0.3f;
   float dx = 0.11f, dy = 0.07f, dz = 0.9f;
-  if (blockIdx.z & 1) { dx = 0.9f; dz = 0.11f; px = 0.3f; pz = tx * pitch; }
+  const int dsel = dirsel < 0 ? (blockIdx.z & 1) : dirsel;
+  if (dsel == 1) { dx = 0.9f; dz = 0.11f; px = 0.3f; pz = tx * pitch; }
+  if (dsel == 2) { dy = 0.9f; dz = 0.07f; py = 0.3f; pz = ty * pitch; dx = 0.11f; }
   const float a = 1.0f / 1024.f;
   for (int i = 0; i < iters; ++i) {
     int x0 = int(px), y0 = int(py), z0 = int(pz);
-    if (x0 >= n - 1 || y0 >= n - 1 || z0 >= n - 1) { px = (tx * pitch) * 0.5f; py = ty * pitch * 0.5f; pz = 0.3f; if (blockIdx.z & 1) { px = 0.3f; pz = tx * pitch * 0.5f; } continue; }
+    if (x0 >= n - 1 || y0 >= n - 1 || z0 >= n - 1) { px = (tx * pitch) * 0.5f; py = ty * pitch * 0.5f; pz = 0.3f; if (dsel == 1) { px = 0.3f; pz = tx * pitch * 0.5f; } if (dsel == 2) { py = 0.3f; pz = ty * pitch * 0.5f; } continue; }
     float* c = vol + ((size_t)x0 * n + y0) * n + z0;
     const size_t sx = (size_t)n * n, sy = n;
-    if (MODE == 0) {
+    if (MODE == 6) {  // 4x4x2 bricks (128-byte lines), separable address f(x)+g(y)+h(z)
+      const unsigned nb = n >> 2, nbz = n >> 1;
+      auto fx = [&](int x) { return (unsigned(x) >> 2) * (nb * nbz * 32u) + (unsigned(x) & 3u) * 8u; };
+      auto fy = [&](int y) { return (unsigned(y) >> 2) * (nbz * 32u) + (unsigned(y) & 3u) * 2u; };
+      auto fz = [&](int z) { return (unsigned(z) >> 1) * 32u + (unsigned(z) & 1u); };
+      const unsigned o = fx(x0) + fy(y0) + fz(z0);
+      const unsigned ex = fx(x0 + 1) - fx(x0), ey = fy(y0 + 1) - fy(y0), ez = fz(z0 + 1) - fz(z0);
+      float* b = vol + o;
+      red1(b, a); red1(b + ez, a); red1(b + ey, a); red1(b + ey + ez, a);
+      red1(b + ex, a); red1(b + ex + ez, a); red1(b + ex + ey, a); red1(b + ex + ey + ez, a);
+    } else if (MODE == 0) {
       red1(c, a); red1(c + 1, a); red1(c + sy, a); red1(c + sy + 1, a);
       red1(c + sx, a); red1(c + sx + 1, a); red1(c + sx + sy, a); red1(c + sx + sy + 1, a);
     } else if (MODE == 1) {
@@ -81,20 +93,20 @@ __global__ void __launch_bounds__(128) k(float* vol, int n, int iters, float pit
 }
 
 template <int MODE>
-float run(float* vol, int n, int iters) {
+float run(float* vol, int n, int iters, int dirsel = -1) {
   dim3 grid(32, 64, 8);  // 512x512 "pixels", 8 "views"
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
-  k<MODE><<<grid, 128>>>(vol, n, iters, 0.45f);
+  k<MODE><<<grid, 128>>>(vol, n, iters, 0.45f, dirsel);
   cudaDeviceSynchronize();
   cudaEventRecord(e0);
-  k<MODE><<<grid, 128>>>(vol, n, iters, 0.45f);
+  k<MODE><<<grid, 128>>>(vol, n, iters, 0.45f, dirsel);
   cudaEventRecord(e1);
   cudaEventSynchronize(e1);
   float ms;
   cudaEventElapsedTime(&ms, e0, e1);
   const double cells = 32.0 * 64 * 8 * 128 * iters;
-  printf("mode %d: %.3f ms, %.1f Gcells/s, %.1f Gcorner-adds/s\n", MODE, ms, cells / ms * 1e-6, 8 * cells / ms * 1e-6);
+  printf("mode %d dir %d: %.3f ms, %.1f Gcells/s, %.1f Gcorner-adds/s\n", MODE, dirsel, ms, cells / ms * 1e-6, 8 * cells / ms * 1e-6);
   return ms;
 }
 
@@ -104,6 +116,8 @@ int main() {
   cudaMalloc(&vol, sizeof(float) * n * n * n);
   cudaMemset(vol, 0, sizeof(float) * n * n * n);
   run<0>(vol, n, iters); run<1>(vol, n, iters); run<2>(vol, n, iters); run<3>(vol, n, iters); run<4>(vol, n, iters); run<5>(vol, n, iters);
+  for (int d = 0; d < 3; ++d) { run<0>(vol, n, iters, d); run<6>(vol, n, iters, d); }
+  run<6>(vol, n, iters);
   cudaError_t e = cudaDeviceSynchronize();
   printf("status: %s\n", cudaGetErrorString(e));
   return e != cudaSuccess;
