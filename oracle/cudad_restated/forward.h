@@ -47,6 +47,10 @@ class fvar {
   __host__ __device__ fvar() : v_{}, d_{} {}
   // implicit promotion of a plain value to a constant (zero tangents)
   __host__ __device__ fvar(const T& v) : v_(v), d_{} {}
+  // value + all tangents (call site: renderer_compareToImage.cuh:19-22)
+  __host__ __device__ fvar(const T& v, const internal::array<T, D>& d) : v_(v), d_{} {
+    for (int i = 0; i < D; ++i) d_[i] = d[i];
+  }
 
   static __host__ __device__ fvar constant(const T& v) { return fvar(v); }
   // seeds the unit tangent e_idx if idx is a valid slot, otherwise a constant
