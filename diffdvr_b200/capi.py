@@ -234,6 +234,12 @@ class Library:
                    P(DvrAdjointOutputs), ctypes.c_void_p])
         self._sig("render_adjoint",
                   [P(DvrInputs), P(DvrOutputs), P(DvrTensor), P(DvrAdjointOutputs), ctypes.c_void_p])
+        # callers either side of the marcher
+        self._sig("generate_rays", [P(DvrTensor), ctypes.c_float, ctypes.c_int32, ctypes.c_int32,
+                                    P(DvrTensor), P(DvrTensor), ctypes.c_void_p])
+        self._sig("generate_rays_adjoint", [P(DvrTensor), ctypes.c_float, P(DvrTensor), P(DvrTensor),
+                                            P(DvrTensor), ctypes.c_void_p])
+        self._sig("compare_to_image", [P(DvrTensor)] * 5 + [ctypes.c_int32, ctypes.c_void_p])
         f = getattr(self.lib, prefix + "last_error")
         f.restype = ctypes.c_char_p
         f.argtypes = []
@@ -272,6 +278,27 @@ class Library:
                        adj: DvrAdjointOutputs, stream: int = 0):
         ci, co, ac = inputs.to_c(), make_outputs(color, termination_index), tensor_view(adj_color)
         self._check(getattr(self.lib, self.prefix + "render_adjoint")(ci, co, ac, adj, stream))
+
+    # -- Camera::generateRays / Renderer::compareToImage --------------------------------------
+    def generate_rays(self, viewport, fov_y_radians, ray_start, ray_dir, stream: int = 0):
+        """viewport B*3*3 -> ray_start, ray_dir B*H*W*3 (written)."""
+        H, W = int(ray_start.shape[1]), int(ray_start.shape[2])
+        self._check(getattr(self.lib, self.prefix + "generate_rays")(
+            tensor_view(viewport), float(fov_y_radians), W, H, tensor_view(ray_start), tensor_view(ray_dir),
+            stream))
+
+    def generate_rays_adjoint(self, viewport, fov_y_radians, adj_ray_start, adj_ray_dir, adj_viewport,
+                              stream: int = 0):
+        """adj_viewport (B*3*3) is overwritten with the per-view sums."""
+        self._check(getattr(self.lib, self.prefix + "generate_rays_adjoint")(
+            tensor_view(viewport), float(fov_y_radians), tensor_view(adj_ray_start), tensor_view(adj_ray_dir),
+            tensor_view(adj_viewport), stream))
+
+    def compare_to_image(self, color_input, gradients_input, color_reference, difference_out, gradients_out,
+                         reduce: bool = False, stream: int = 0):
+        self._check(getattr(self.lib, self.prefix + "compare_to_image")(
+            tensor_view(color_input), tensor_view(gradients_input), tensor_view(color_reference),
+            tensor_view(difference_out), tensor_view(gradients_out), int(bool(reduce)), stream))
 
 
 _PRODUCT: Optional["ProductLibrary"] = None

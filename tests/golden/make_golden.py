@@ -11,6 +11,9 @@ Run in the build container (needs /root/reference and `make -C oracle ref`):
   instantiated over the restated cudAD of oracle/cudad_restated) on the seeded scenes of
   tests/scenes.py. The scene INPUTS are regenerated from the seed by the tests; only the outputs are
   stored.
+* ``ref_camera_*.npz``: Camera::generateRays (forward + backward) and Renderer::compareToImage from the
+  same library (oracle/ref_shim_camera.cpp: the reference's CameraEval / adjNormalize / adjCross /
+  CompareToImage headers) on the seeded inputs of tests/camera_cases.py.
 * ``NonConvexDensity.tsv``: copied verbatim from /root/reference/unittests/NonConvexDensity.tsv
   (the reference's committed known-answer table, generator unittests/testNonConvexDensity.cpp:8-80).
 """
@@ -23,6 +26,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
 sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+import camera_cases  # noqa: E402
 import golden_cases  # noqa: E402
 import oracle_loader as ol  # noqa: E402
 import scenes  # noqa: E402
@@ -37,6 +41,18 @@ def main():
         out = golden_cases.run(ref, sc, flags, fg)
         np.savez_compressed(os.path.join(HERE, f"ref_{name}.npz"), **out)
         print(name, {k: v.shape for k, v in out.items()})
+    # Camera::generateRays / compareToImage built on the reference's own headers (ref_shim_camera.cpp)
+    for name, case in camera_cases.ray_cases().items():
+        path = os.path.join(HERE, f"ref_camera_{name}.npz")
+        if not os.path.exists(path) or "--all" in sys.argv:
+            out = camera_cases.run_rays(ref, case)
+            np.savez_compressed(path, **{k: out[k] for k in ("viewport", "ray_start", "ray_dir", "adj_viewport")})
+            print(name)
+    for name, case in camera_cases.compare_cases().items():
+        path = os.path.join(HERE, f"ref_camera_{name}.npz")
+        if not os.path.exists(path) or "--all" in sys.argv:
+            np.savez_compressed(path, **camera_cases.run_compare(ref, case))
+            print(name)
     src = "/root/reference/unittests/NonConvexDensity.tsv"
     if os.path.exists(src):
         shutil.copyfile(src, os.path.join(HERE, "NonConvexDensity.tsv"))
