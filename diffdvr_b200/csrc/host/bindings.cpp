@@ -12,6 +12,7 @@
 
 #include "../../../include/dvr_b200.h"
 #include "renderer.h"
+#include "camera.h"
 
 namespace py = pybind11;
 using namespace renderer;
@@ -236,7 +237,38 @@ PYBIND11_MODULE(pyrenderer, m) {
       .def_static("forward_variables_to_gradients", &Renderer::forwardVariablesToGradients,
                   py::doc("Contracts the forward variables with the adjoint colour into camera/stepsize/TF adjoints."),
                   py::arg("forward_variables"), py::arg("adj_color"), py::arg("differences_settings"),
-                  py::arg("adj_outputs"));
+                  py::arg("adj_outputs"))
+      // C++-only in the reference (renderer/renderer.h:228-250); exposed here for scripting and tests
+      .def_static("compare_to_image", &Renderer::compareToImage,
+                  py::doc("L2 norm |color_input - color_reference| and its forward derivatives, per pixel or reduced."),
+                  py::arg("color_input"), py::arg("gradients_input"), py::arg("color_reference"),
+                  py::arg("difference_out"), py::arg("gradients_out"), py::arg("reduce") = false);
+
+  // ---- camera (bindings.cpp:514-551) ------------------------------------------------------------
+  py::enum_<Camera::Orientation>(m, "Orientation")
+      .value("Xp", Camera::Xp)
+      .value("Xm", Camera::Xm)
+      .value("Yp", Camera::Yp)
+      .value("Ym", Camera::Ym)
+      .value("Zp", Camera::Zp)
+      .value("Zm", Camera::Zm);
+
+  py::class_<Camera>(m, "Camera")
+      .def_static("compute_matrix", &Camera::computeInverseViewProjectionMatrix,
+                  py::doc("Computes the inverse view-projection matrix. Not differentiable!"), py::arg("origin"),
+                  py::arg("look_at"), py::arg("up"), py::arg("fov_degrees"), py::arg("width"), py::arg("height"),
+                  py::arg("near_clip") = 0.1f, py::arg("far_clip") = 10.0f)
+      .def_static("generate_rays", &Camera::generateRays,
+                  py::doc("Per-pixel rays (ray_start, ray_dir: B*H*W*3) from the viewport matrix B*3*3 "
+                          "(eye, right, up). Differentiable with respect to the viewport."),
+                  py::arg("viewport"), py::arg("fovY"), py::arg("screen_width"), py::arg("screen_height"))
+      .def_static("viewport_from_lookat", &Camera::viewportFromLookAt,
+                  py::doc("Viewport matrix for generate_rays() from origin, look-at target and up vector."),
+                  py::arg("origin"), py::arg("look_at"), py::arg("camera_up"))
+      .def_static("viewport_from_sphere", &Camera::viewportFromSphere,
+                  py::doc("Viewport matrix for generate_rays() from a position on the sphere around a center."),
+                  py::arg("center"), py::arg("yaw_radians"), py::arg("pitch_radians"), py::arg("distance"),
+                  py::arg("orientation"));
 
   // ---- timing (bindings.cpp:554-558) ------------------------------------------------------------
   py::class_<GPUTimer>(m, "GpuTimer")

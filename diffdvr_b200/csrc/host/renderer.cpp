@@ -254,4 +254,19 @@ void Renderer::renderAdjoint(const RendererInputsHost& inputsHost, const Rendere
   raise_on_error(dvr_render_adjoint(&in, &fwd, &ac, &adj, current_stream(dev)));
 }
 
+void Renderer::compareToImage(const torch::Tensor& colorInput, const torch::Tensor& gradientsInput,
+                              const torch::Tensor& colorReference, torch::Tensor& differenceOut,
+                              torch::Tensor& gradientsOut, bool reduce) {
+  DVR_CHECK_DEFINED(colorInput, "colorInput");
+  TORCH_CHECK(colorInput.device().is_cuda(), "colorInput is a CPU tensor: this build has no CPU back-end");
+  const torch::Device dev = colorInput.device();
+  const c10::cuda::CUDAGuard guard(dev);
+  const DvrTensor c = real_view(colorInput, "colorInput", dev);
+  const DvrTensor g = real_view(gradientsInput, "gradientsInput", dev);
+  const DvrTensor r = real_view(colorReference, "colorReference", dev);
+  const DvrTensor d = real_view(differenceOut, "differenceOut", dev);
+  const DvrTensor o = real_view(gradientsOut, "gradientsOut", dev);
+  raise_on_error(dvr_compare_to_image(&c, &g, &r, &d, &o, reduce ? 1 : 0, current_stream(dev)));
+}
+
 }  // namespace renderer

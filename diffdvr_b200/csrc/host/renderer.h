@@ -139,6 +139,13 @@ class Renderer {
   static void renderAdjoint(const RendererInputsHost& inputsHost, const RendererOutputsHost& outputsFromForwardHost,
                             const torch::Tensor& adj_color, AdjointOutputsHost& adj_outputs);
 
+  // renderer/renderer.h:228-250: L2 norm between colorInput and colorReference with its D forward
+  // derivatives, per pixel (differenceOut B*H*W*1, gradientsOut B*H*W*D) or averaged over the image
+  // (shapes 1 and D). Any D (the reference's CUDA path only runs D == 1).
+  static void compareToImage(const torch::Tensor& colorInput, const torch::Tensor& gradientsInput,
+                             const torch::Tensor& colorReference, torch::Tensor& differenceOut,
+                             torch::Tensor& gradientsOut, bool reduce = false);
+
   // extensions (not in the reference): library options of include/dvr_b200.h
   static void setOption(const std::string& name, int value);
   static int getOption(const std::string& name);

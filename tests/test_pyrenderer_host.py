@@ -118,3 +118,79 @@ def test_options_and_control_shims():
     pyr.set_cuda_debug_mode(False)
     assert pyr.has_variant(pyr.VolumeFilterMode.Trilinear, pyr.CameraMode.ReferenceFrame, pyr.TFMode.Texture,
                            pyr.BlendMode.BeerLambert)
+
+
+# ---- Camera (bindings/bindings.cpp:514-551) ----------------------------------------------------------
+def test_camera_surface():
+    for name in ("Xp", "Xm", "Yp", "Ym", "Zp", "Zm"):
+        assert hasattr(pyr.Orientation, name)
+    for f in ("compute_matrix", "generate_rays", "viewport_from_lookat", "viewport_from_sphere"):
+        assert callable(getattr(pyr.Camera, f)), f
+    assert callable(pyr.Renderer.compare_to_image)
+
+
+def test_viewport_from_lookat_matches_numpy_restatement():
+    import camera_cases as cc
+    rng = np.random.RandomState(2)
+    origin, look_at = rng.uniform(-2, 2, (4, 3)).astype(np.float32), rng.uniform(-0.2, 0.2, (4, 3)).astype(np.float32)
+    up = np.tile(np.array([[0, 1, 0]], np.float32), (4, 1))
+    got = pyr.Camera.viewport_from_lookat(torch.from_numpy(origin), torch.from_numpy(look_at), torch.from_numpy(up))
+    want = cc.viewport_from_lookat(origin.astype(np.float64), look_at.astype(np.float64), up.astype(np.float64))
+    assert got.shape == (4, 3, 3)
+    assert np.allclose(got.numpy(), want, atol=1e-6)
+    # right-handed-looking frame of the reference: right = normalize(front x up), up2 = normalize(right x front)
+    front = look_at - origin
+    front /= np.linalg.norm(front, axis=1, keepdims=True)
+    assert np.allclose(np.cross(got[:, 1].numpy(), front), got[:, 2].numpy(), atol=1e-5)
+
+
+def test_viewport_from_sphere_semantics_and_autograd():
+    # pytests/diffdvr/utils.py + renderer/camera.cpp:141-180: Ym orientation, yaw inverted, permutation (-1,-2,-3)
+    center = torch.zeros(2, 3)
+    yaw = torch.tensor([[0.3], [1.1]], requires_grad=True)
+    pitch = torch.tensor([[0.2], [-0.4]], requires_grad=True)
+    dist = torch.tensor([[1.5], [2.0]])
+    vp = pyr.Camera.viewport_from_sphere(center, yaw, pitch, dist, pyr.Orientation.Ym)
+    assert vp.shape == (2, 3, 3)
+    # OrientationInvertPitch is false for every orientation: the pitch is always negated (camera.cpp:160)
+    y, p, d = yaw.detach().numpy(), -pitch.detach().numpy(), dist.numpy()
+    pos = np.concatenate([np.cos(p) * np.cos(y) * d, np.sin(p) * d, np.cos(p) * np.sin(y) * d], axis=1)
+    assert np.allclose(vp[:, 0].detach().numpy(), -pos, atol=1e-6)  # origin = -pos for Ym (yaw * +1)
+    assert np.allclose(np.linalg.norm(vp[:, 1].detach().numpy(), axis=1), 1, atol=1e-6)
+    assert np.allclose((vp[:, 1] * vp[:, 2]).sum(1).detach().numpy(), 0, atol=1e-6)
+    vp.square().sum().backward()
+    assert yaw.grad is not None and pitch.grad is not None and torch.isfinite(yaw.grad).all()
+    # Yp: yaw sign flipped (OrientationInvertYaw false -> * -1), identity permutation
+    vp2 = pyr.Camera.viewport_from_sphere(center, yaw.detach(), pitch.detach(), dist, pyr.Orientation.Yp)
+    pos2 = np.concatenate([np.cos(p) * np.cos(-y) * d, np.sin(p) * d, np.cos(p) * np.sin(-y) * d], axis=1)
+    assert np.allclose(vp2[:, 0].numpy(), pos2, atol=1e-6)
+
+
+def test_compute_matrix_is_the_inverse_view_projection():
+    o, la, up = (-1.0, -0.5, 0.2), (0.0, 0.0, 0.0), (0.0, 0.0, 1.0)  # unittests/testConsistencyTF.cpp scene camera
+    m = np.array(pyr.Camera.compute_matrix(pyr.real3(*o), pyr.real3(*la), pyr.real3(*up), 45.0, 128, 64, 0.1, 10.0))
+    assert m.shape == (4, 4)
+    o, la, up = (np.array(v, np.float64) for v in (o, la, up))
+    f = (la - o) / np.linalg.norm(la - o)
+    s = np.cross(up, f)
+    s /= np.linalg.norm(s)
+    u = np.cross(f, s)
+    view = np.eye(4)
+    view[0, :3], view[1, :3], view[2, :3] = s, u, f
+    view[:3, 3] = [-s @ o, -u @ o, -f @ o]
+    h = 1 / np.tan(np.radians(45.0) / 2)
+    proj = np.zeros((4, 4))
+    proj[0, 0], proj[1, 1] = h * 64 / 128, h
+    proj[2, 2], proj[2, 3], proj[3, 2] = 10 / 9.9, -(10 * 0.1) / 9.9, 1
+    assert np.allclose(m, np.linalg.inv(proj @ view), rtol=1e-5, atol=1e-5)
+    # NDC (0, 0, z=0) unprojects onto the near plane straight ahead of the eye (matmul_proj semantics)
+    w = m @ np.array([0, 0, 0, 1.0])
+    assert np.allclose(w[:3] / w[3], o + 0.1 * f, atol=1e-5)
+
+
+def test_generate_rays_rejects_cpu_tensors():
+    with pytest.raises(RuntimeError, match="no CPU back-end"):
+        pyr.Camera.generate_rays(torch.zeros(1, 3, 3), 0.5, 8, 8)
+    with pytest.raises(RuntimeError, match="no CPU back-end"):
+        pyr.Renderer.compare_to_image(torch.zeros(1, 2, 2, 4), torch.zeros(1, 2, 2, 1, 4), torch.zeros(1, 2, 2, 4),
+                                      torch.zeros(1, 2, 2, 1), torch.zeros(1, 2, 2, 1), False)
