@@ -118,3 +118,83 @@ def test_launches_go_to_the_current_torch_stream_and_timer_works():
     pyr.Renderer.render_forward(inp, out)
     t.stop()
     assert 0.0 < t.elapsed_ms() < 1000.0
+
+
+# ---- Camera / compareToImage through the host layer --------------------------
+def test_generate_rays_autograd_matches_capi_and_oracle():
+    import camera_cases as cc
+    import oracle_loader as ol
+    case = cc.ray_cases()["rays_packed"]
+    want = cc.run_rays(ol.port(32), case)
+    vp = torch.from_numpy(want["viewport"]).cuda().requires_grad_(True)
+    start, direction = pyr.Camera.generate_rays(vp, case["fovY"], case["W"], case["H"])
+    assert start.shape == (case["B"], case["H"], case["W"], 3)
+    assert np.array_equal(start.detach().cpu().numpy(), want["ray_start"])
+    assert scenes.rel_l2(direction.detach().cpu().numpy(), want["ray_dir"]) <= 1e-6
+    gs, gd = torch.from_numpy(want["adj_ray_start"]).cuda(), torch.from_numpy(want["adj_ray_dir"]).cuda()
+    ((start * gs).sum() + (direction * gd).sum()).backward()
+    assert scenes.rel_l2(vp.grad.cpu().numpy(), want["adj_viewport"]) <= 1e-4
+    # only one of the two outputs reaches the loss
+    vp2 = vp.detach().clone().requires_grad_(True)
+    _, d2 = pyr.Camera.generate_rays(vp2, case["fovY"], case["W"], case["H"])
+    (d2 * gd).sum().backward()
+    assert torch.isfinite(vp2.grad).all() and (vp2.grad[:, 0] == 0).all()  # eye does not influence directions
+
+
+def test_sphere_camera_to_adjoint_chain_matches_finite_differences():
+    """run_entropy2d-style chain: (yaw, pitch) -> viewport_from_sphere -> generate_rays -> render -> loss;
+    d loss / d (yaw, pitch) through render_adjoint(camera) + autograd against central differences."""
+    sc = scenes.make_scene(n=24, W=32, H=24, B=1, camera_mode=capi.CAMERA_RAY_START_DIR, tf_mode=capi.TF_GAUSSIAN, R=3,
+                           seed=9, opacity=6.0)
+    fov, W, H = 0.7, sc.W, sc.H
+    center = torch.zeros(1, 3, device="cuda")
+    dist = torch.tensor([[1.6]], device="cuda")
+    weight = torch.rand(1, H, W, 4, generator=torch.Generator().manual_seed(0)).cuda()
+
+    def render(yaw, pitch, with_grad):
+        vp = pyr.Camera.viewport_from_sphere(center, yaw, pitch, dist, pyr.Orientation.Ym)
+        start, direction = pyr.Camera.generate_rays(vp, fov, W, H)
+        inp = pr.make_inputs(sc)
+        inp.camera = pyr.CameraPerPixelRays(start.detach(), direction.detach())
+        out = pyr.RendererOutputs(torch.empty(1, H, W, 4, device="cuda"),
+                                  torch.empty(1, H, W, dtype=torch.int32, device="cuda"))
+        pyr.Renderer.render_forward(inp, out)
+        loss = (out.color.double() * weight).sum().item()
+        if not with_grad:
+            return loss
+        a, o = pr._adjoint_outputs(1, H, W, camera=True)
+        pyr.Renderer.render_adjoint(inp, out, weight, a)
+        torch.autograd.backward([start, direction], [o["adj_camera_ray_start"], o["adj_camera_ray_dir"]])
+        return loss
+
+    yaw = torch.tensor([[0.4]], device="cuda", requires_grad=True)
+    pitch = torch.tensor([[0.3]], device="cuda", requires_grad=True)
+    render(yaw, pitch, True)
+    eps = 2e-3
+    fd_yaw = (render(yaw.detach() + eps, pitch.detach(), False) - render(yaw.detach() - eps, pitch.detach(), False)) / (2 * eps)
+    fd_pitch = (render(yaw.detach(), pitch.detach() + eps, False) - render(yaw.detach(), pitch.detach() - eps, False)) / (2 * eps)
+    got = np.array([yaw.grad.item(), pitch.grad.item()])
+    want = np.array([fd_yaw, fd_pitch])
+    assert np.linalg.norm(got - want) <= 5e-2 * np.linalg.norm(want), (got, want)
+
+
+def test_compare_to_image_through_host_layer():
+    import camera_cases as cc
+    import oracle_loader as ol
+    case = cc.compare_cases()["compare_d6"]
+    want = cc.run_compare(ol.port(32), case)
+    rng = np.random.RandomState(cc.SEED + 1)
+    B, W, H, D = case["B"], case["W"], case["H"], case["D"]
+    color = torch.from_numpy(rng.uniform(0, 1, (B, H, W, 4)).astype(np.float32)).cuda()
+    reference = torch.from_numpy(rng.uniform(0, 1, (B, H, W, 4)).astype(np.float32)).cuda()
+    grads = torch.from_numpy(rng.standard_normal((B, H, W, D, 4)).astype(np.float32)).cuda()
+    diff, gout = torch.empty(B, H, W, 1, device="cuda"), torch.empty(B, H, W, D, device="cuda")
+    pyr.Renderer.compare_to_image(color, grads, reference, diff, gout, False)
+    dr, gr_ = torch.empty(1, device="cuda"), torch.empty(D, device="cuda")
+    pyr.Renderer.compare_to_image(color, grads, reference, dr, gr_, True)
+    assert scenes.rel_l2(diff.cpu().numpy(), want["difference"]) <= 1e-6
+    assert scenes.rel_l2(gout.cpu().numpy(), want["gradients"]) <= 1e-6
+    assert scenes.rel_l2(dr.cpu().numpy(), want["difference_reduced"]) <= 1e-4
+    assert scenes.rel_l2(gr_.cpu().numpy(), want["gradients_reduced"]) <= 1e-4
+    with pytest.raises(RuntimeError):  # wrong output shape for the reduced variant
+        pyr.Renderer.compare_to_image(color, grads, reference, diff, gout, True)
