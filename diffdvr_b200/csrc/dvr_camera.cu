@@ -51,11 +51,11 @@ __global__ void __launch_bounds__(256) k_generate_rays(const GenRaysArgs a) {
   const int b = blockIdx.z;
   const Frame f = load_frame(a, b);
   const int per = a.packed ? 4 : 1;
-  const long long items = (long long)a.W * a.H / per;
-  const long long it = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned items = unsigned(a.W) * unsigned(a.H) / per;  // W*H < 2^31 (checked by the C-ABI)
+  const unsigned it = blockIdx.x * blockDim.x + threadIdx.x;
   if (it >= items) return;
-  const long long pix = it * per;
-  const int y = int(pix / a.W), x0 = int(pix - (long long)y * a.W);
+  const unsigned pix = it * per;
+  const int y = int(pix / unsigned(a.W)), x0 = int(pix - unsigned(y) * unsigned(a.W));
   float d[12];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
@@ -102,14 +102,13 @@ __global__ void __launch_bounds__(256) k_generate_rays_adjoint(const GenRaysArgs
   const int b = blockIdx.z;
   const Frame f = load_frame(a, b);
   const int per = a.packed ? 4 : 1;
-  const long long items = (long long)a.W * a.H / per;
+  const unsigned items = unsigned(a.W) * unsigned(a.H) / per;
   float acc[12];
 #pragma unroll
   for (int i = 0; i < 12; ++i) acc[i] = 0.f;
-  for (long long it = (long long)blockIdx.x * blockDim.x + threadIdx.x; it < items;
-       it += (long long)gridDim.x * blockDim.x) {
-    const long long pix = it * per;
-    const int y = int(pix / a.W), x0 = int(pix - (long long)y * a.W);
+  for (unsigned it = blockIdx.x * blockDim.x + threadIdx.x; it < items; it += gridDim.x * blockDim.x) {
+    const unsigned pix = it * per;
+    const int y = int(pix / unsigned(a.W)), x0 = int(pix - unsigned(y) * unsigned(a.W));
     float gs[12], gd[12];
     if (a.packed) {
       const float4* ps = reinterpret_cast<const float4*>(a.rayStart + ((long long)b * a.H * a.W + pix) * 3);
@@ -195,20 +194,19 @@ __global__ void __launch_bounds__(256) k_compare_to_image(const CompareArgs a) {
     for (int i = threadIdx.x; i <= a.D; i += blockDim.x) s_sum[i] = 0.f;
     __syncthreads();
   }
-  const long long plane = (long long)a.W * a.H, total = plane * a.B;
+  const unsigned plane = unsigned(a.W) * unsigned(a.H);  // < 2^31 (checked by the C-ABI)
   const int lane = threadIdx.x & 31;
+  const int b = blockIdx.z;
   // uniform trip count: every lane takes part in the shuffles of the reduced variant
-  const long long span = (long long)gridDim.x * blockDim.x;
-  const long long rounds = (total + span - 1) / span;
-  for (long long r = 0; r < rounds; ++r) {
-    const long long i = r * span + (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const bool active = i < total;
-    int b = 0, y = 0, x = 0;
+  const unsigned span = gridDim.x * blockDim.x;
+  const unsigned rounds = (plane + span - 1) / span;
+  for (unsigned r = 0; r < rounds; ++r) {
+    const unsigned i = r * span + blockIdx.x * blockDim.x + threadIdx.x;
+    const bool active = i < plane;
+    int y = 0, x = 0;
     if (active) {
-      b = int(i / plane);
-      const long long rem = i - b * plane;
-      y = int(rem / a.W);
-      x = int(rem - (long long)y * a.W);
+      y = int(i / unsigned(a.W));
+      x = int(i - unsigned(y) * unsigned(a.W));
     }
     f4 diff = {0.f, 0.f, 0.f, 0.f};
     float len = 0.f;
@@ -264,15 +262,17 @@ cudaError_t launch_generate_rays_adjoint(const GenRaysArgs& a, cudaStream_t s) {
 }
 
 cudaError_t launch_compare_to_image(const CompareArgs& a, cudaStream_t s) {
-  const long long total = (long long)a.W * a.H * a.B;
-  long long blocks = (total + 255) / 256;
+  const long long plane = (long long)a.W * a.H;
+  long long blocks = (plane + 255) / 256;
   if (a.reduce) {
     cudaError_t e = launch_kernel(k_zero_compare, dim3((a.D + 256) / 256), 256, 0, s, a);
     if (e != cudaSuccess) return e;
-    if (blocks > 148 * 8) blocks = 148 * 8;  // one wave of 8 CTAs per SM, grid-stride inside
+    // about one wave of 8 CTAs per SM over all views, grid-stride inside a view
+    const long long cap = (148 * 8 + a.B - 1) / a.B;
+    if (blocks > cap) blocks = cap;
   }
   const size_t smem = a.reduce ? size_t(a.D + 1) * sizeof(float) : 0;
-  return launch_kernel(k_compare_to_image, dim3((unsigned)blocks), 256, smem, s, a);
+  return launch_kernel(k_compare_to_image, dim3((unsigned)blocks, 1, a.B), 256, smem, s, a);
 }
 
 }  // namespace dvr

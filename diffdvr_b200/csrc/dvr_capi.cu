@@ -341,6 +341,7 @@ void fill_gen_rays(const DvrTensor& viewport, float fovY, int W, int H, const Dv
   const int B = int(viewport.size[0]);
   if (W <= 0 || H <= 0) fail(DVR_ERR_INVALID_ARGUMENT, "screen size must be positive, but is (%d, %d)", W, H);
   if (B < 1 || B > 65535) fail(DVR_ERR_UNSUPPORTED, "batch size %d outside [1, 65535]", B);
+  if ((long long)W * H >= (1ll << 31)) fail(DVR_ERR_UNSUPPORTED, "screen size %d x %d exceeds 2^31 pixels", W, H);
   const DvrTensor* ts[2] = {&start, &dir};
   const char* names[2] = {nameStart, nameDir};
   for (int k = 0; k < 2; ++k) {
@@ -681,6 +682,8 @@ int dvr_compare_to_image(const DvrTensor* color, const DvrTensor* grads, const D
       a.qB = grads_out->stride[0]; a.qY = grads_out->stride[1]; a.qX = grads_out->stride[2]; a.qD = grads_out->stride[3];
     }
     if ((long long)B * H * W == 0) return;
+    if (B > 65535) fail(DVR_ERR_UNSUPPORTED, "batch size %d exceeds 65535", B);
+    if ((long long)W * H >= (1ll << 31)) fail(DVR_ERR_UNSUPPORTED, "screen size %d x %d exceeds 2^31 pixels", W, H);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     cuda_check(launch_compare_to_image(a, s), "dvr_compare_to_image");
     if (a.reduce) g_launches.fetch_add(1, std::memory_order_relaxed);  // zero + reduce

@@ -141,9 +141,12 @@ def test_generate_rays_autograd_matches_capi_and_oracle():
     assert torch.isfinite(vp2.grad).all() and (vp2.grad[:, 0] == 0).all()  # eye does not influence directions
 
 
-def test_sphere_camera_to_adjoint_chain_matches_finite_differences():
-    """run_entropy2d-style chain: (yaw, pitch) -> viewport_from_sphere -> generate_rays -> render -> loss;
-    d loss / d (yaw, pitch) through render_adjoint(camera) + autograd against central differences."""
+def test_sphere_camera_to_adjoint_chain():
+    """run_entropy2d-style chain: (yaw, pitch) -> viewport_from_sphere -> generate_rays -> render -> loss.
+    d loss / d (yaw, pitch) = <adj_rays from render_adjoint(camera), d rays / d (yaw, pitch)>; the second factor
+    is checked by central differences of the (smooth) ray generator, the first is pinned by the adjoint tests.
+    (Differencing the RENDER itself is no oracle here: like the reference, the adjoint treats the box entry
+    parameter tmin as a constant, renderer_kernels.cuh:336-345.)"""
     sc = scenes.make_scene(n=24, W=32, H=24, B=1, camera_mode=capi.CAMERA_RAY_START_DIR, tf_mode=capi.TF_GAUSSIAN, R=3,
                            seed=9, opacity=6.0)
     fov, W, H = 0.7, sc.W, sc.H
@@ -151,31 +154,38 @@ def test_sphere_camera_to_adjoint_chain_matches_finite_differences():
     dist = torch.tensor([[1.6]], device="cuda")
     weight = torch.rand(1, H, W, 4, generator=torch.Generator().manual_seed(0)).cuda()
 
-    def render(yaw, pitch, with_grad):
+    def rays(yaw, pitch):
         vp = pyr.Camera.viewport_from_sphere(center, yaw, pitch, dist, pyr.Orientation.Ym)
-        start, direction = pyr.Camera.generate_rays(vp, fov, W, H)
-        inp = pr.make_inputs(sc)
-        inp.camera = pyr.CameraPerPixelRays(start.detach(), direction.detach())
-        out = pyr.RendererOutputs(torch.empty(1, H, W, 4, device="cuda"),
-                                  torch.empty(1, H, W, dtype=torch.int32, device="cuda"))
-        pyr.Renderer.render_forward(inp, out)
-        loss = (out.color.double() * weight).sum().item()
-        if not with_grad:
-            return loss
-        a, o = pr._adjoint_outputs(1, H, W, camera=True)
-        pyr.Renderer.render_adjoint(inp, out, weight, a)
-        torch.autograd.backward([start, direction], [o["adj_camera_ray_start"], o["adj_camera_ray_dir"]])
-        return loss
+        return pyr.Camera.generate_rays(vp, fov, W, H)
 
     yaw = torch.tensor([[0.4]], device="cuda", requires_grad=True)
     pitch = torch.tensor([[0.3]], device="cuda", requires_grad=True)
-    render(yaw, pitch, True)
-    eps = 2e-3
-    fd_yaw = (render(yaw.detach() + eps, pitch.detach(), False) - render(yaw.detach() - eps, pitch.detach(), False)) / (2 * eps)
-    fd_pitch = (render(yaw.detach(), pitch.detach() + eps, False) - render(yaw.detach(), pitch.detach() - eps, False)) / (2 * eps)
+    start, direction = rays(yaw, pitch)
+    inp = pr.make_inputs(sc)
+    inp.camera = pyr.CameraPerPixelRays(start.detach(), direction.detach())
+    out = pyr.RendererOutputs(torch.empty(1, H, W, 4, device="cuda"),
+                              torch.empty(1, H, W, dtype=torch.int32, device="cuda"))
+    pyr.Renderer.render_forward(inp, out)
+    assert out.color[..., 3].max().item() > 0.1  # the volume is in view
+    a, o = pr._adjoint_outputs(1, H, W, camera=True)
+    pyr.Renderer.render_adjoint(inp, out, weight, a)
+    adj_s, adj_d = o["adj_camera_ray_start"], o["adj_camera_ray_dir"]
+    assert adj_d.abs().max().item() > 0
+    torch.autograd.backward([start, direction], [adj_s, adj_d])
+
+    eps = 1e-3
+    want = []
+    for which in (0, 1):
+        dy = eps if which == 0 else 0.0
+        dp = eps if which == 1 else 0.0
+        with torch.no_grad():
+            s1, d1 = rays(yaw + dy, pitch + dp)
+            s0, d0 = rays(yaw - dy, pitch - dp)
+        want.append((((s1 - s0).double() / (2 * eps)) * adj_s.double()).sum().item() +
+                    (((d1 - d0).double() / (2 * eps)) * adj_d.double()).sum().item())
     got = np.array([yaw.grad.item(), pitch.grad.item()])
-    want = np.array([fd_yaw, fd_pitch])
-    assert np.linalg.norm(got - want) <= 5e-2 * np.linalg.norm(want), (got, want)
+    want = np.array(want)
+    assert np.linalg.norm(got - want) <= 2e-3 * np.linalg.norm(want), (got, want)
 
 
 def test_compare_to_image_through_host_layer():
