@@ -57,6 +57,9 @@ template <int N> DVR_DEV Du<N> operator/(const Du<N>& a, const Du<N>& b) {
 template <int N> DVR_DEV Du<N> operator/(const Du<N>& a, float b) { return a * (1.0f / b); }
 template <int N> DVR_DEV Du<N> du_exp(const Du<N>& a) { Du<N> r; r.v = expf(a.v); DVR_DU_LOOP r.d[i] = a.d[i] * r.v; return r; }
 DVR_DEV float du_exp(float a) { return expf(a); }
+// exp of the Beer-Lambert blend: the same blend_exp as the plain forward kernel, so both write the same colour
+template <int N> DVR_DEV Du<N> du_blend_exp(const Du<N>& a) { Du<N> r; r.v = blend_exp(a.v); DVR_DU_LOOP r.d[i] = a.d[i] * r.v; return r; }
+DVR_DEV float du_blend_exp(float a) { return blend_exp(a); }
 // selection rules of the restated cudAD (oracle/cudad_restated/forward.h): a<b ? a : b
 template <int N> DVR_DEV Du<N> du_min(const Du<N>& a, const Du<N>& b) { return a.v < b.v ? a : b; }
 template <int N> DVR_DEV Du<N> du_max(const Du<N>& a, const Du<N>& b) { return a.v > b.v ? a : b; }
@@ -183,11 +186,11 @@ __global__ void __launch_bounds__(kThreads) k_forward_gradients(const RayInputs 
                      du_lerp(du_lerp(d[1], d[5], fxd), du_lerp(d[3], d[7], fxd), fyd), fzd);
       }
       cur = tf_eval_dual<TF, N, HAS_TF>(s_tf, s_dtf, in.R, dd, d0);
-      if constexpr (BLEND == kBlendBeer) alpha = 1.0f - du_exp(-(cur.w * step));
+      if constexpr (BLEND == kBlendBeer) alpha = 1.0f - du_blend_exp(-(cur.w * step));
       else alpha = du_min(du_const<N>(1.f), cur.w * step);
     } else {
       cur = tf_eval_dual<TF, N, HAS_TF>(s_tf, s_dtf, in.R, density, d0);
-      if constexpr (BLEND == kBlendBeer) alpha = 1.0f - du_exp(-(cur.w * ray.step));
+      if constexpr (BLEND == kBlendBeer) alpha = 1.0f - du_blend_exp(-(cur.w * ray.step));
       else alpha = du_min(du_const<N>(1.f), cur.w * ray.step);
     }
     // Blending::blend generic (renderer_blending.cuh:40-51, 105-116)
