@@ -45,6 +45,9 @@ cudaError_t DVR_NAME(DVR_TF, DVR_BL)(int filter, bool hasVol, int tfacc, bool ha
   if (filter == kFilterTrilinear)
     return hasVol ? by_acc<kFilterTrilinear, true>(tfacc, hasRay, in, aa, grid, smem, s)
                   : by_acc<kFilterTrilinear, false>(tfacc, hasRay, in, aa, grid, smem, s);
+  if (filter == kFilterTrilinearQuad)
+    return hasVol ? by_acc<kFilterTrilinearQuad, true>(tfacc, hasRay, in, aa, grid, smem, s)
+                  : by_acc<kFilterTrilinearQuad, false>(tfacc, hasRay, in, aa, grid, smem, s);
   return cudaErrorInvalidValue;
 }
 

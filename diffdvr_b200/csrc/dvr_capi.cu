@@ -368,6 +368,55 @@ void fill_gen_rays(const DvrTensor& viewport, float fovY, int W, int H, const Dv
   a.packed = W % 4 == 0 && packed(start) && packed(dir);
 }
 
+// ---- QUAD copy of the volume (RayInputs::quads) ------------------------------------------------
+// Stream-ordered scratch from the device's default memory pool (cudaMallocAsync / cudaFreeAsync): no
+// library-owned cache, safe with concurrent streams; the pool keeps the pages between calls once its
+// release threshold is raised. Option "volume_layout": 0 never, 1 always (trilinear), -1 automatic.
+struct QuadScratch {
+  float4* ptr = nullptr;
+  cudaStream_t stream = nullptr;
+  ~QuadScratch() {
+    if (ptr) cudaFreeAsync(ptr, stream);
+  }
+};
+
+void raise_pool_threshold() {
+  static std::atomic<unsigned long long> done{0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev >= 64) return;
+  if (done.load() & (1ull << dev)) return;
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+    unsigned long long keep = ~0ull;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+  }
+  done.fetch_or(1ull << dev);
+}
+
+// returns the filter id to dispatch on (kFilterTrilinearQuad if the copy was built)
+int maybe_build_quads(int filter, Checked& c, QuadScratch& q, cudaStream_t s) {
+  if (filter != DVR_FILTER_TRILINEAR) return filter;
+  const int opt = g_volume_layout.load();
+  if (opt == 0) return filter;
+  const long long voxels = (long long)c.X * c.Y * c.Z;
+  const int nb = c.ri.volB == 0 ? 1 : c.B;
+  if (voxels >= (1ll << 31) || c.X < 2 || c.Y < 2 || c.Z < 2) return filter;
+  // automatic: the copy costs ~5 volume sweeps; worth it once the rays visit about as many cells as there are voxels
+  if (opt < 0 && (long long)c.B * c.W * c.H * 64 < voxels * nb) return filter;
+  raise_pool_threshold();
+  void* p = nullptr;
+  if (cudaMallocAsync(&p, size_t(voxels) * nb * sizeof(float4), s) != cudaSuccess) {
+    cudaGetLastError();  // out of memory: sample the caller's tensor directly
+    return filter;
+  }
+  q.ptr = static_cast<float4*>(p);
+  q.stream = s;
+  after_launch(launch_build_quads(c.ri, nb, q.ptr, s), "dvr_build_quads", s);
+  c.ri.quads = q.ptr;
+  c.ri.quadB = nb == 1 ? 0 : voxels;
+  return kFilterTrilinearQuad;
+}
+
 }  // namespace
 
 namespace dvr {
@@ -422,7 +471,9 @@ int dvr_render_forward(const DvrInputs* inputs, const DvrOutputs* outputs, void*
       return;
     }
     const size_t smem = check_smem(size_t(c.ri.R) * tf_row(inputs->tf_mode) * sizeof(float));
-    after_launch(launch_forward(inputs->volume_filter_mode, inputs->tf_mode, inputs->blend_mode, c.ri, fo,
+    QuadScratch quads;
+    const int filter = maybe_build_quads(inputs->volume_filter_mode, c, quads, s);
+    after_launch(launch_forward(filter, inputs->tf_mode, inputs->blend_mode, c.ri, fo,
                                 tile_grid(c), smem, s),
                  "dvr_render_forward", s);
   });
@@ -478,7 +529,9 @@ int dvr_render_adjoint(const DvrInputs* inputs, const DvrOutputs* fwd, const Dvr
     const int ntab = tfacc == kTfAccSmem ? kThreads / 32 : (tfacc == kTfAccReg ? 1 : 0);
     const size_t smem =
         check_smem((size_t((c.ri.R * tf_row(tf) + 3) & ~3) + size_t(ntab) * entries) * sizeof(float));
-    after_launch(launch_adjoint(inputs->volume_filter_mode, tf, inputs->blend_mode, hasVol, tfacc, hasRay, c.ri, aa,
+    QuadScratch quads;
+    const int filter = maybe_build_quads(inputs->volume_filter_mode, c, quads, s);
+    after_launch(launch_adjoint(filter, tf, inputs->blend_mode, hasVol, tfacc, hasRay, c.ri, aa,
                                 tile_grid(c), smem, s),
                  "dvr_render_adjoint", s);
   });

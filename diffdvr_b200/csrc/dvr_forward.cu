@@ -1,4 +1,4 @@
-// Instances of the plain forward kernel: {Nearest, Trilinear} x {Identity, Texture, Linear,
+// Instances of the plain forward kernel: {Nearest, Trilinear, Trilinear on the QUAD copy} x {Identity, Texture, Linear,
 // Gaussian, GaussianLog} x {BeerLambert, Alpha}. The camera mode is a run-time switch outside
 // the marching loop, so the reference's 3 camera instantiations collapse into one.
 #include "dvr_kernels.cuh"
@@ -25,6 +25,8 @@ cudaError_t launch_forward(int filter, int tf, int blend, const RayInputs& in, c
   if (filter == kFilterNearest && blend == kBlendAlpha) return by_tf<kFilterNearest, kBlendAlpha>(tf, in, out, grid, smem, s);
   if (filter == kFilterTrilinear && blend == kBlendBeer) return by_tf<kFilterTrilinear, kBlendBeer>(tf, in, out, grid, smem, s);
   if (filter == kFilterTrilinear && blend == kBlendAlpha) return by_tf<kFilterTrilinear, kBlendAlpha>(tf, in, out, grid, smem, s);
+  if (filter == kFilterTrilinearQuad && blend == kBlendBeer) return by_tf<kFilterTrilinearQuad, kBlendBeer>(tf, in, out, grid, smem, s);
+  if (filter == kFilterTrilinearQuad && blend == kBlendAlpha) return by_tf<kFilterTrilinearQuad, kBlendAlpha>(tf, in, out, grid, smem, s);
   return cudaErrorInvalidValue;
 }
 

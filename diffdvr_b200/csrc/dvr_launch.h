@@ -34,6 +34,9 @@ cudaError_t launch_fwdvars_to_gradients(const FwdVarsArgs& a, cudaStream_t strea
 cudaError_t launch_count_cells(const RayInputs& in, const int* term, long long tB, long long tY, long long tX,
                                unsigned long long* counts, dim3 grid, cudaStream_t stream);
 
+// QUAD copy of the volume for kFilterTrilinearQuad (dvr_misc.cu): nb batch entries of X*Y*Z float4
+cudaError_t launch_build_quads(const RayInputs& in, int nb, float4* quads, cudaStream_t stream);
+
 // Camera::generateRays forward / adjoint and Renderer::compareToImage (dvr_camera.cu)
 cudaError_t launch_generate_rays(const GenRaysArgs& a, cudaStream_t stream);
 cudaError_t launch_generate_rays_adjoint(const GenRaysArgs& a, cudaStream_t stream);  // 2 launches

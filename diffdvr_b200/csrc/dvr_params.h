@@ -15,6 +15,9 @@ constexpr int kThreads = 128;
 
 // numeric enum values of renderer/renderer_settings.cuh:81-146
 enum : int { kFilterNearest = 0, kFilterTrilinear = 1, kFilterPreshaded = 3 };
+// internal: trilinear sampling of the library's own QUAD copy of the volume (RayInputs::quads), chosen by the
+// host dispatch (dvr_capi.cu); never part of the C-ABI
+enum : int { kFilterTrilinearQuad = 101 };
 enum : int { kCamRays = 0, kCamInvView = 1, kCamFrame = 2 };
 enum : int { kTfIdentity = 0, kTfTexture = 1, kTfLinear = 2, kTfGaussian = 3, kTfPreshaded = 5, kTfGaussianLog = 6 };
 enum : int { kBlendBeer = 0, kBlendAlpha = 1 };
@@ -31,6 +34,10 @@ struct RayInputs {
   const float* volume;
   long long volB;
   int sx, sy, sz;
+  // QUAD copy (kFilterTrilinearQuad): Q[b][x][y][z] = (v[y][z], v[y][z'], v[y'][z], v[y'][z']) of slice x with
+  // y' = min(y+1, Y-1), z' = min(z+1, Z-1): one cell = 2 aligned 16-byte loads (x and min(x+1, X-1))
+  const float4* quads;
+  long long quadB;                   // float4 elements per batch entry (0: one volume for all views)
   Strided1 boxMin, boxSize;          // p == nullptr -> use the *V value
   float boxMinV[3], boxSizeV[3];
   int cameraMode;

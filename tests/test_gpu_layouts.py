@@ -1,0 +1,61 @@
+"""GPU: the two volume layouts of the trilinear sampler -- the caller's strided tensor sampled in place
+("volume_layout" = 0) and the library's QUAD copy (= 1; two 16-byte loads per cell) -- give the same results:
+the forward image bit-for-bit (same corner values, same arithmetic), the gradients up to atomic summation order;
+both against the golden fixtures of the reference's compiled kernels."""
+import os
+
+import numpy as np
+import pytest
+
+import golden_cases
+import gpu_runner as gr
+import scenes
+from diffdvr_b200 import capi
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CASES = {name: (sc, flags, fg) for name, sc, flags, fg in golden_cases.cases()
+         if sc.filter_mode == capi.FILTER_TRILINEAR}
+
+
+def _run(layout, sc, flags, gold):
+    lib = capi.load()
+    lib.set_option("volume_layout", layout)
+    lib.set_option("compat_stepsize_overwrite", 1)
+    try:
+        n0 = lib.launch_count()
+        color, term = gr.forward(sc, lib)
+        launches = lib.launch_count() - n0
+        adj_color = np.random.RandomState(golden_cases.ADJ_SEED).randn(*color.shape).astype(np.float32)
+        adj = gr.adjoint(sc, gold["color"], gold["term"], adj_color, lib=lib, **flags)
+    finally:
+        lib.set_option("volume_layout", -1)
+        lib.set_option("compat_stepsize_overwrite", 0)
+    return color, term, adj, launches
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_quad_copy_equals_in_place_sampling(name):
+    sc, flags, _ = CASES[name]
+    gold = np.load(os.path.join(GOLDEN, f"ref_{name}.npz"))
+    c0, t0, a0, l0 = _run(0, sc, flags, gold)
+    c1, t1, a1, l1 = _run(1, sc, flags, gold)
+    assert l0 == 1 and l1 == 2  # the copy is one extra launch
+    assert np.array_equal(c0, c1) and np.array_equal(t0, t1)
+    assert scenes.rel_l2(c1, gold["color"]) <= 1e-5
+    for k in a0:
+        assert scenes.rel_l2(a1[k], a0[k]) <= 2e-6, k
+    for k in ("adj_volume", "adj_tf"):
+        if k in a1:
+            assert scenes.rel_l2(a1[k], gold[k]) <= 1e-4, k
+
+
+def test_automatic_choice_follows_the_work_estimate():
+    lib = capi.load()
+    assert lib.get_option("volume_layout") == -1
+    big = scenes.make_scene(n=48, W=4, H=4, B=1, seed=1)      # 16 rays, 110592 voxels: in place
+    small = scenes.make_scene(n=16, W=32, H=32, B=1, seed=1)  # 1024 rays, 4096 voxels: copy
+    for sc, want in ((big, 1), (small, 2)):
+        n0 = lib.launch_count()
+        gr.forward(sc, lib)
+        assert lib.launch_count() - n0 == want
