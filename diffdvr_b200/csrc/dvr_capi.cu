@@ -529,11 +529,30 @@ int dvr_render_adjoint(const DvrInputs* inputs, const DvrOutputs* fwd, const Dvr
     const int ntab = tfacc == kTfAccSmem ? kThreads / 32 : (tfacc == kTfAccReg ? 1 : 0);
     const size_t smem =
         check_smem((size_t((c.ri.R * tf_row(tf) + 3) & ~3) + size_t(ntab) * entries) * sizeof(float));
-    QuadScratch quads;
-    const int filter = maybe_build_quads(inputs->volume_filter_mode, c, quads, s);
+    QuadScratch quads, gradQuads;
+    int filter = maybe_build_quads(inputs->volume_filter_mode, c, quads, s);
+    int ng = 0;
+    if (filter == kFilterTrilinearQuad && hasVol) {
+      // gradient scratch in the same layout: 2 x red.v4 per cell instead of 8 scalar REDs, folded afterwards
+      const long long voxels = (long long)c.X * c.Y * c.Z;
+      ng = aa.avB == 0 ? 1 : c.B;
+      void* p = nullptr;
+      const size_t bytes = size_t(voxels) * ng * sizeof(float4);
+      if (cudaMallocAsync(&p, bytes, s) == cudaSuccess) {
+        gradQuads.ptr = static_cast<float4*>(p);
+        gradQuads.stream = s;
+        cuda_check(cudaMemsetAsync(p, 0, bytes, s), "dvr_render_adjoint");
+        aa.gradQuads = gradQuads.ptr;
+        aa.gradQuadB = ng == 1 ? 0 : voxels;
+      } else {
+        cudaGetLastError();
+        filter = inputs->volume_filter_mode;  // not enough memory for the scratch: in-place path
+      }
+    }
     after_launch(launch_adjoint(filter, tf, inputs->blend_mode, hasVol, tfacc, hasRay, c.ri, aa,
                                 tile_grid(c), smem, s),
                  "dvr_render_adjoint", s);
+    if (aa.gradQuads) after_launch(launch_fold_quads(c.ri, aa, ng, s), "dvr_fold_quads", s);
   });
 }
 

@@ -294,7 +294,10 @@ __global__ void __launch_bounds__(kThreads) k_adjoint(const RayInputs in, const 
     float adjStep = 0.f;
     f3 adjStart = {0.f, 0.f, 0.f}, adjDir = {0.f, 0.f, 0.f};
     Sampler<FILTER, HAS_VOL> smp;
-    smp.init(in, b, aa.adjVolume, aa.avB);
+    if constexpr (FILTER == kFilterTrilinearQuad && HAS_VOL)
+      smp.init(in, b, reinterpret_cast<float*>(aa.gradQuads), aa.gradQuadB * 4);
+    else
+      smp.init(in, b, aa.adjVolume, aa.avB);
     // terminationIndex-1 was the last sample that contributed (renderer_kernels.cuh:374-376)
     float fi = float(n - 1);
     for (int i = n - 1; i >= 0; --i, fi -= 1.0f) {

@@ -36,6 +36,8 @@ cudaError_t launch_count_cells(const RayInputs& in, const int* term, long long t
 
 // QUAD copy of the volume for kFilterTrilinearQuad (dvr_misc.cu): nb batch entries of X*Y*Z float4
 cudaError_t launch_build_quads(const RayInputs& in, int nb, float4* quads, cudaStream_t stream);
+// adjVolume[b][x][y][z] += the four quad components that target voxel (x, y, z); nb gradient volumes
+cudaError_t launch_fold_quads(const RayInputs& in, const AdjointArgs& aa, int nb, cudaStream_t stream);
 
 // Camera::generateRays forward / adjoint and Renderer::compareToImage (dvr_camera.cu)
 cudaError_t launch_generate_rays(const GenRaysArgs& a, cudaStream_t stream);

@@ -101,6 +101,47 @@ __global__ void __launch_bounds__(256) k_build_quads(const RayInputs in, float4*
   quads[(size_t)b * n + i] = q;
 }
 
+// Folds the QUAD gradient scratch into the caller's adj_volume (accumulating, like the atomics it replaces).
+// Component k of G[x][y][z] targets voxel (x, y + (k>>1 clamped), z + (k&1 clamped)); as a gather per voxel:
+//   .x of (y, z), .y of (y, z-1), .z of (y-1, z), .w of (y-1, z-1), plus the components that the clamp at the
+//   far faces folds back onto the voxel itself (z = Z-1: .y/.w of the same z; y = Y-1: .z/.w of the same y).
+__global__ void __launch_bounds__(256) k_fold_quads(const RayInputs in, const AdjointArgs aa) {
+  const unsigned n = unsigned(in.X) * unsigned(in.Y) * unsigned(in.Z);
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int b = blockIdx.z;
+  const unsigned Z = unsigned(in.Z), Y = unsigned(in.Y);
+  const unsigned z = i % Z, xy = i / Z;
+  const unsigned y = xy % Y, x = xy / Y;
+  const float4* g = aa.gradQuads + (size_t)b * aa.gradQuadB;
+  const bool zl = z == Z - 1, yl = y == Y - 1;
+  const float4 q = g[i];
+  float s = q.x;
+  if (zl) s += q.y;
+  if (yl) s += q.z;
+  if (zl && yl) s += q.w;
+  if (z > 0) {
+    const float4 r = g[i - 1];
+    s += r.y;
+    if (yl) s += r.w;
+  }
+  if (y > 0) {
+    const float4 r = g[i - Z];
+    s += r.z;
+    if (zl) s += r.w;
+  }
+  if (y > 0 && z > 0) s += g[i - Z - 1].w;
+  if (s != 0.f) {
+    float* p = aa.adjVolume + b * aa.avB + (long long)x * aa.avx + (long long)y * aa.avy + (long long)z * aa.avz;
+    *p += s;
+  }
+}
+
+cudaError_t launch_fold_quads(const RayInputs& in, const AdjointArgs& aa, int nb, cudaStream_t s) {
+  const unsigned n = unsigned(in.X) * unsigned(in.Y) * unsigned(in.Z);
+  return launch_kernel(k_fold_quads, dim3((n + 255) / 256, 1, nb), 256, 0, s, in, aa);
+}
+
 cudaError_t launch_build_quads(const RayInputs& in, int nb, float4* quads, cudaStream_t s) {
   const unsigned n = unsigned(in.X) * unsigned(in.Y) * unsigned(in.Z);
   return launch_kernel(k_build_quads, dim3((n + 255) / 256, 1, nb), 256, 0, s, in, quads);

@@ -71,6 +71,11 @@ struct AdjointArgs {
   long long avB;
   int avx, avy, avz;
   int sameStrides;                   // adj_volume has the element strides of the volume
+  // kFilterTrilinearQuad + hasVolume: gradients are accumulated into a zeroed QUAD scratch
+  // G[b][x][y][z] = (g(y,z), g(y,z'), g(y',z), g(y',z')) with 2 x red.v4 per cell and folded into adjVolume
+  // by k_fold_quads afterwards
+  float4* gradQuads;
+  long long gradQuadB;               // float4 elements per batch entry (0: one gradient volume for all views)
   float* adjStep;
   long long asB, asY, asX;
   int stepAtomic;                    // broadcasting -> atomics (renderer_kernels.cuh:418-421)
