@@ -356,12 +356,15 @@ def run_ours(a):
             "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": dict(workload_config(a), l2="256 MiB L2 flush between timed steps; per-step working set "
-                           "(volume 64 MiB + adj_volume 64 MiB + images) also exceeds the 126 MB L2"),
+                           "(volume 64 MiB + its QUAD copy 256 MiB + QUAD gradient scratch 256 MiB + adj_volume 64 MiB + images) "
+                           "also exceeds the 126 MB L2"),
             "fwd_gsamples_per_s": samples_per_launch / (fwd_ms * 1e-3) / 1e9,
             "adj_gsamples_per_s": samples_per_launch / (adj_ms * 1e-3) / 1e9,
             "fwd_ms_per_launch": fwd_ms, "adj_ms_per_launch": adj_ms,
             "samples_per_step": n_samples, "cell_visits_per_step": n_cells,
-            "roofline": {"kernel": "k_adjoint<Trilinear,Identity,BeerLambert,hasVol>", "bound": "hbm",
+            "roofline": {"kernel": "k_adjoint<TrilinearQuad,Identity,BeerLambert,hasVol>", "bound": "hbm",
+                         "duration": "CUDA events around the whole dvr_render_adjoint call: QUAD copy + memset + "
+                                     "march + gradient fold (the march is 97 % of it, profiles/r01_summary.md)",
                          "achieved": achieved, "peak": peak,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650",
                          "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
