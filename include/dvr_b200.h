@@ -20,6 +20,7 @@
  *    (renderer/renderer_settings.cuh:81-146);
  *  - adjoint outputs are ACCUMULATED into caller-zeroed tensors
  *    (renderer/renderer_settings.cuh:227-229);
+ *  - no device allocations except the stream-ordered scratch of "volume_layout" (below);
  *  - every function returns DVR_OK (0) or a negative error code, never throws;
  *    dvr_last_error() returns a thread-local message for the last failure;
  *  - launches are asynchronous on `stream` (a cudaStream_t passed as void*), like the
@@ -227,9 +228,15 @@ DVR_API int dvr_has_variant(int32_t volume_filter_mode, int32_t camera_mode, int
  *                                    renderer/renderer_kernels.cuh:393-395 with
  *                                    renderer/renderer_blending.cuh:93,158); 0 (default)
  *                                    accumulates it (mathematically complete gradient).
- *   "volume_layout"             0 = sample the caller's strided tensor directly,
- *                               1 = re-brick into the internal tiled layout per call,
- *                               -1 (default) = automatic
+ *   "volume_layout"             trilinear forward / adjoint:
+ *                               0 = sample the caller's strided tensor in place (8 x 4-byte loads
+ *                                   and 8 scalar REDs per cell),
+ *                               1 = build a QUAD copy of the volume per call (16 bytes per voxel
+ *                                   holding the (y,z) 2x2 footprint: 2 x 16-byte loads per cell) and,
+ *                                   in the adjoint, accumulate into a QUAD scratch with 2 x red.v4
+ *                                   per cell that is folded into adj_volume afterwards; scratch is
+ *                                   stream-ordered (cudaMallocAsync on `stream`),
+ *                               -1 (default) = automatic: 1 when rays * 64 >= voxels
  * Returns DVR_OK or DVR_ERR_INVALID_ARGUMENT for an unknown name. */
 DVR_API int dvr_set_option(const char* name, int32_t value);
 DVR_API int dvr_get_option(const char* name, int32_t* value);
