@@ -139,8 +139,35 @@ struct TfGrad {
 };
 
 // adjoint of tf_eval; returns adj_density and adds the parameter adjoints to `acc`
+// Gaussian TF: the adjoint needs the same exp(-(d-mu)^2 / 2 sigma^2) per row as the evaluation; the first
+// kRegRows of them are kept in registers between the two (the precise expf is ~10 instructions).
+template <int TF>
+DVR_DEV f4 tf_eval_cached(const float* s_tf, int R, float density, float (&ni)[kRegRows]) {
+  if constexpr (TF == kTfGaussian) {
+    f4 c = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int i = 0; i < kRegRows; ++i) {
+      ni[i] = 0.f;
+      if (i < R) {
+        const f4 ci = lds4(s_tf + 8 * i);
+        ni[i] = expf(gauss_arg(density, s_tf + 8 * i));
+        c.x = fmaf(ci.x, ni[i], c.x); c.y = fmaf(ci.y, ni[i], c.y); c.z = fmaf(ci.z, ni[i], c.z); c.w = fmaf(ci.w, ni[i], c.w);
+      }
+    }
+    for (int i = kRegRows; i < R; ++i) {
+      const f4 ci = lds4(s_tf + 8 * i);
+      const float n = expf(gauss_arg(density, s_tf + 8 * i));
+      c.x = fmaf(ci.x, n, c.x); c.y = fmaf(ci.y, n, c.y); c.z = fmaf(ci.z, n, c.z); c.w = fmaf(ci.w, n, c.w);
+    }
+    return c;
+  } else {
+    return tf_eval<TF>(s_tf, R, density);
+  }
+}
+
 template <int TF, int TFACC>
-DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC, TfGrad<TF, TFACC>& acc) {
+DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC, TfGrad<TF, TFACC>& acc,
+                         const float (&cache)[kRegRows]) {
   constexpr bool HAS_TF = TFACC != kTfAccNone;
   if constexpr (TF == kTfIdentity) {  // renderer_tf.cuh:75-104
     const float dc = fmaxf(0.f, fminf(density, 1.f));
@@ -183,11 +210,10 @@ DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC
     return adjFrac / (p1 - p0);  // passes through the clamp unconditionally ("#if 1", :350-352)
   } else if constexpr (TF == kTfGaussian) {  // :562-614
     float adjDensity = 0.f;
-    auto body = [&](int i, float* g) {
+    auto body = [&](int i, float* g, float ni) {
       const f4 ci = lds4(s_tf + 8 * i);
       const float mu = s_tf[8 * i + 4], sigma = s_tf[8 * i + 5];
-      const float ni = expf(gauss_arg(density, mu, sigma));
-      const float f1 = (mu - density) / (sigma * sigma) * ni;
+      const float f1 = div_rcp(mu - density, sigma * sigma, s_tf[8 * i + 7]) * ni;
       const float dc = dot4(adjC, ci);
       adjDensity = fmaf(dc, f1, adjDensity);
       if constexpr (HAS_TF) {
@@ -202,14 +228,21 @@ DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC
       for (int i = 0; i < kRegRows; ++i)
         if (i < R) {
           float g[6];
-          body(i, g);
+          body(i, g, cache[i]);
 #pragma unroll
           for (int c = 0; c < 6; ++c) acc.g[i * 6 + c] += g[c];
         }
     } else {
-      for (int i = 0; i < R; ++i) {
+#pragma unroll
+      for (int i = 0; i < kRegRows; ++i)
+        if (i < R) {
+          float g[6];
+          body(i, g, cache[i]);
+          if constexpr (HAS_TF) acc.add_row(i, g);
+        }
+      for (int i = kRegRows; i < R; ++i) {
         float g[6];
-        body(i, g);
+        body(i, g, expf(gauss_arg(density, s_tf + 8 * i)));
         if constexpr (HAS_TF) acc.add_row(i, g);
       }
     }
@@ -218,7 +251,7 @@ DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC
     float adjDensity = 0.f;
     auto tval = [&](int i) {
       const f4 ci = lds4(s_tf + 8 * i);
-      const float ln = gauss_arg(density, s_tf[8 * i + 4], s_tf[8 * i + 5]);
+      const float ln = gauss_arg(density, s_tf + 8 * i);
       return f4{logf(ci.x) + ln, logf(ci.y) + ln, logf(ci.z) + ln, logf(ci.w) + ln};
     };
     auto body = [&](int i, float* g) {
@@ -232,7 +265,7 @@ DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC
           den.x += expf(tj.x - ti.x); den.y += expf(tj.y - ti.y); den.z += expf(tj.z - ti.z); den.w += expf(tj.w - ti.w);
         }
       const f4 adjTi = {adjC.x / den.x, adjC.y / den.y, adjC.z / den.z, adjC.w / den.w};
-      const float f1 = (mu - density) / (sigma * sigma);
+      const float f1 = div_rcp(mu - density, sigma * sigma, s_tf[8 * i + 7]);
       const float adjXmu = adjTi.x * f1 + adjTi.y * f1 + adjTi.z * f1 + adjTi.w * f1;
       adjDensity += adjXmu;
       if constexpr (HAS_TF) {
@@ -304,11 +337,12 @@ __global__ void __launch_bounds__(kThreads) k_adjoint(const RayInputs in, const 
       const float t = sample_t(ray, fi);
       const f3 p = sample_pos<HAS_RAY>(ray, t);
       const float density = smp.fetch(in, &aa, p.x, p.y, p.z);
-      const f4 cur = tf_eval<TF>(s_tf, in.R, density);
+      float tfCache[kRegRows];
+      const f4 cur = tf_eval_cached<TF>(s_tf, in.R, density, tfCache);
       f4 adjCur;
       float adjStepBlend;
       blend_adjoint<BLEND>(acc, adjAcc, cur, ray.step, adjCur, adjStepBlend);
-      const float adjDensity = tf_adjoint<TF, TFACC>(s_tf, in.R, density, adjCur, tfg);
+      const float adjDensity = tf_adjoint<TF, TFACC>(s_tf, in.R, density, adjCur, tfg, tfCache);
       const f3 g = smp.template adjoint<HAS_RAY>(adjDensity);
       if constexpr (HAS_RAY) {
         // the reference overwrites its accumulator with the blend term (see compat flag)
