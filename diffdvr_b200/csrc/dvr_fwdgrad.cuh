@@ -78,9 +78,16 @@ template <int N> struct Du4 { Du<N> x, y, z, w; };
 template <int TF, int N, bool HAS_TF, typename DENS>
 DVR_DEV Du4<N> tf_eval_dual(const float* s_tf, const int* s_dtf, int R, const DENS& density, int d0) {
   constexpr int ROW = TfLayout<TF>::kRow;
+  // TF entries are dual numbers only when TF derivatives are traced; otherwise plain floats, so that the
+  // products below are Du x float (N multiplies) instead of Du x Du with N zero tangents (2N FMAs that the
+  // compiler may not fold: x * 0 is not 0 for NaN / inf)
   auto seed = [&](int r, int c) {
     if constexpr (HAS_TF) return du_input<N>(s_tf[r * ROW + c], s_dtf[r * ROW + c], d0);
-    else return du_const<N>(s_tf[r * ROW + c]);
+    else return s_tf[r * ROW + c];
+  };
+  auto to_du = [&](auto v) {
+    if constexpr (sizeof(v) == sizeof(float)) return du_const<N>(v);
+    else return v;
   };
   auto dens = [&]() {
     if constexpr (sizeof(DENS) == sizeof(float)) return du_const<N>(density);
@@ -88,7 +95,7 @@ DVR_DEV Du4<N> tf_eval_dual(const float* s_tf, const int* s_dtf, int R, const DE
   };
   if constexpr (TF == kTfIdentity) {
     const Du<N> dc = du_clamp(dens(), du_const<N>(0.f), du_const<N>(1.f));
-    const Du<N> sa = seed(0, 0), sc = seed(0, 1);
+    const auto sa = seed(0, 0), sc = seed(0, 1);
     const Du<N> col = dc * sc;
     return {col, col, col, dc * sa};
   } else if constexpr (TF == kTfTexture) {
@@ -101,7 +108,7 @@ DVR_DEV Du4<N> tf_eval_dual(const float* s_tf, const int* s_dtf, int R, const DE
   } else if constexpr (TF == kTfLinear) {
     const Du<N> dd = dens();
     const int i = linear_interval(s_tf, R, dd.v);
-    const Du<N> p0 = seed(i, 4), p1 = seed(i + 1, 4);
+    const Du<N> p0 = to_du(seed(i, 4)), p1 = to_du(seed(i + 1, 4));
     const Du<N> d2 = du_clamp(dd, p0, p1);
     const Du<N> frac = (d2 - p0) / (p1 - p0);
     return {du_lerp(seed(i, 0), seed(i + 1, 0), frac), du_lerp(seed(i, 1), seed(i + 1, 1), frac),
@@ -110,7 +117,7 @@ DVR_DEV Du4<N> tf_eval_dual(const float* s_tf, const int* s_dtf, int R, const DE
     const Du<N> dd = dens();
     Du4<N> c = {du_const<N>(0.f), du_const<N>(0.f), du_const<N>(0.f), du_const<N>(0.f)};
     for (int i = 0; i < R; ++i) {
-      const Du<N> mu = seed(i, 4), sigma = seed(i, 5);
+      const auto mu = seed(i, 4), sigma = seed(i, 5);
       const Du<N> diff = dd - mu;
       const Du<N> ni = du_exp(-(diff * diff) / (2.0f * sigma * sigma));
       c.x = c.x + seed(i, 0) * ni;
