@@ -240,6 +240,9 @@ class Library:
         self._sig("generate_rays_adjoint", [P(DvrTensor), ctypes.c_float, P(DvrTensor), P(DvrTensor),
                                             P(DvrTensor), ctypes.c_void_p])
         self._sig("compare_to_image", [P(DvrTensor)] * 5 + [ctypes.c_int32, ctypes.c_void_p])
+        self._sig("preshade_volume", [P(DvrTensor), P(DvrTensor), ctypes.c_int32, P(DvrTensor), ctypes.c_void_p])
+        self._sig("preshade_volume_adjoint", [P(DvrTensor), P(DvrTensor), ctypes.c_int32, P(DvrTensor), P(DvrTensor),
+                                              ctypes.c_void_p])
         f = getattr(self.lib, prefix + "last_error")
         f.restype = ctypes.c_char_p
         f.argtypes = []
@@ -299,6 +302,18 @@ class Library:
         self._check(getattr(self.lib, self.prefix + "compare_to_image")(
             tensor_view(color_input), tensor_view(gradients_input), tensor_view(color_reference),
             tensor_view(difference_out), tensor_view(gradients_out), int(bool(reduce)), stream))
+
+    # -- TFUtils::preshadeVolume --------------------------------------------------------------------
+    def preshade_volume(self, density_volume, tf, tf_mode, color_out, stream: int = 0):
+        """density_volume 1*X*Y*Z, tf 1*R*C -> color_out 4*X*Y*Z (written)."""
+        self._check(getattr(self.lib, self.prefix + "preshade_volume")(
+            tensor_view(density_volume), tensor_view(tf), int(tf_mode), tensor_view(color_out), stream))
+
+    def preshade_volume_adjoint(self, density_volume, tf, tf_mode, adj_color, adj_volume_out, stream: int = 0):
+        """adj_volume_out (1*X*Y*Z) is overwritten."""
+        self._check(getattr(self.lib, self.prefix + "preshade_volume_adjoint")(
+            tensor_view(density_volume), tensor_view(tf), int(tf_mode), tensor_view(adj_color),
+            tensor_view(adj_volume_out), stream))
 
 
 _PRODUCT: Optional["ProductLibrary"] = None

@@ -763,6 +763,74 @@ int dvr_compare_to_image(const DvrTensor* color, const DvrTensor* grads, const D
   });
 }
 
+// shared by the two preshade entry points: PreshadeVolumeFunction::forward checks (renderer/tf_utils.cpp:180-214)
+static void fill_preshade(const DvrTensor& vol, const DvrTensor& tf, int tfMode, const DvrTensor& color,
+                          const char* colorName, RayInputs& in, PreshadeArgs& a, size_t& smem) {
+  std::memset(&in, 0, sizeof(in));
+  std::memset(&a, 0, sizeof(a));
+  check_dim(vol, "densityVolume", 4);
+  check_size(vol, "densityVolume", 0, 1);
+  const long long X = vol.size[1], Y = vol.size[2], Z = vol.size[3];
+  if (X < 1 || Y < 1 || Z < 1) fail(DVR_ERR_INVALID_ARGUMENT, "densityVolume must not be empty");
+  if (X * Y * Z >= (1ll << 31)) fail(DVR_ERR_UNSUPPORTED, "densityVolume must have fewer than 2^31 voxels");
+  check_dim(tf, "tf", 3);
+  check_size(tf, "tf", 0, 1);
+  switch (tfMode) {
+    case DVR_TF_IDENTITY: check_size(tf, "tf", 1, 1); check_size(tf, "tf", 2, 2); break;
+    case DVR_TF_TEXTURE: check_size(tf, "tf", 2, 4); break;
+    case DVR_TF_LINEAR: check_size(tf, "tf", 2, 5); break;
+    case DVR_TF_GAUSSIAN:
+    case DVR_TF_GAUSSIAN_LOG: check_size(tf, "tf", 2, 6); break;
+    default: fail(DVR_ERR_INVALID_ARGUMENT, "unknown tf enum value");
+  }
+  if (tf.size[1] < (tfMode == DVR_TF_LINEAR ? 2 : 1)) fail(DVR_ERR_INVALID_ARGUMENT, "tensor 'tf' has too few rows");
+  check_dim(color, colorName, 4);
+  check_size(color, colorName, 0, 4);
+  check_size(color, colorName, 1, X);
+  check_size(color, colorName, 2, Y);
+  check_size(color, colorName, 3, Z);
+  in.X = int(X); in.Y = int(Y); in.Z = int(Z);
+  in.volume = static_cast<const float*>(vol.ptr);
+  in.sx = int(vol.stride[1]); in.sy = int(vol.stride[2]); in.sz = int(vol.stride[3]);
+  in.tf = {static_cast<const float*>(tf.ptr), 0, tf.stride[1], tf.stride[2]};
+  in.R = int(tf.size[1]);
+  in.C = int(tf.size[2]);
+  a.color = static_cast<float*>(color.ptr);
+  a.cC = color.stride[0]; a.cX = color.stride[1]; a.cY = color.stride[2]; a.cZ = color.stride[3];
+  smem = check_smem(size_t(in.R) * tf_row(tfMode) * sizeof(float));
+}
+
+int dvr_preshade_volume(const DvrTensor* vol, const DvrTensor* tf, int32_t tf_mode, const DvrTensor* color_out,
+                        void* stream) {
+  return guarded([&] {
+    if (!vol || !tf || !color_out) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    RayInputs in;
+    PreshadeArgs a;
+    size_t smem;
+    fill_preshade(*vol, *tf, tf_mode, *color_out, "colorVolume", in, a, smem);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    after_launch(launch_preshade(tf_mode, false, in, a, smem, s), "dvr_preshade_volume", s);
+  });
+}
+
+int dvr_preshade_volume_adjoint(const DvrTensor* vol, const DvrTensor* tf, int32_t tf_mode, const DvrTensor* adj_color,
+                                const DvrTensor* adj_volume_out, void* stream) {
+  return guarded([&] {
+    if (!vol || !tf || !adj_color || !adj_volume_out) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    RayInputs in;
+    PreshadeArgs a;
+    size_t smem;
+    fill_preshade(*vol, *tf, tf_mode, *adj_color, "adj_colorVolume", in, a, smem);
+    check_dim(*adj_volume_out, "adj_densityVolume", 4);
+    check_size(*adj_volume_out, "adj_densityVolume", 0, 1);
+    for (int d = 1; d < 4; ++d) check_size(*adj_volume_out, "adj_densityVolume", d, vol->size[d]);
+    a.adjVolume = static_cast<float*>(adj_volume_out->ptr);
+    a.ax = adj_volume_out->stride[1]; a.ay = adj_volume_out->stride[2]; a.az = adj_volume_out->stride[3];
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    after_launch(launch_preshade(tf_mode, true, in, a, smem, s), "dvr_preshade_volume_adjoint", s);
+  });
+}
+
 int dvr_count_cell_visits(const DvrInputs* inputs, const DvrTensor* termination_index, uint64_t* counts,
                           void* stream) {
   return guarded([&] {

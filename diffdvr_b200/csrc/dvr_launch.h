@@ -44,6 +44,10 @@ cudaError_t launch_generate_rays(const GenRaysArgs& a, cudaStream_t stream);
 cudaError_t launch_generate_rays_adjoint(const GenRaysArgs& a, cudaStream_t stream);  // 2 launches
 cudaError_t launch_compare_to_image(const CompareArgs& a, cudaStream_t stream);       // reduce: 2 launches
 
+// TFUtils::preshadeVolume forward / adjoint (dvr_tfutils.cu)
+cudaError_t launch_preshade(int tf, bool adjoint, const RayInputs& in, const PreshadeArgs& a, size_t smem,
+                            cudaStream_t stream);
+
 // per-(tf, blend) translation units (parallel compilation)
 #define DVR_DECL_ADJ(TF, BL)                                                                          \
   cudaError_t launch_adjoint_##TF##_##BL(int filter, bool hasVol, int tfacc, bool hasRay,             \

@@ -150,4 +150,13 @@ struct CompareArgs {
   long long qB, qY, qX, qD;
 };
 
+// TFUtils::preshadeVolume forward / adjoint (renderer/tf_utils_impl.cu:16-92, 98-183). The density volume and
+// the TF travel in a RayInputs (volume, X/Y/Z, strides, tf, R, C; everything else unused).
+struct PreshadeArgs {
+  float* color;                      // forward: 4*X*Y*Z written; adjoint: adj_color read
+  long long cC, cX, cY, cZ;
+  float* adjVolume;                  // adjoint: 1*X*Y*Z, overwritten
+  long long ax, ay, az;
+};
+
 }  // namespace dvr

@@ -201,6 +201,20 @@ DVR_API int dvr_compare_to_image(const DvrTensor* color_input, const DvrTensor* 
                          const DvrTensor* color_reference, const DvrTensor* difference_out,
                          const DvrTensor* gradients_out, int32_t reduce, void* stream);
 
+/* TFUtils::preshadeVolume (renderer/tf_utils.cpp:172-300 -> kernel::PreshadeVolume,
+ * renderer/tf_utils_impl.cu:16-92): color_out[c][x][y][z] = TF(density_volume[0][x][y][z]), the input of
+ * the DVR_FILTER_PRESHADED / DVR_TF_PRESHADED marcher. density_volume 1*X*Y*Z, tf 1*R*C of `tf_mode`
+ * (Identity, Texture, Linear, Gaussian, GaussianLog), color_out 4*X*Y*Z (r, g, b, absorption). */
+DVR_API int dvr_preshade_volume(const DvrTensor* density_volume, const DvrTensor* tf, int32_t tf_mode,
+                        const DvrTensor* color_out, void* stream);
+
+/* Its adjoint with respect to the density (kernel::PreshadeVolumeAdj, renderer/tf_utils_impl.cu:98-183):
+ * adj_volume_out[0][x][y][z] = <adj_color[:, x, y, z], dTF/d density>; OVERWRITTEN like the reference
+ * (no TF adjoint there either). */
+DVR_API int dvr_preshade_volume_adjoint(const DvrTensor* density_volume, const DvrTensor* tf, int32_t tf_mode,
+                                const DvrTensor* adj_color, const DvrTensor* adj_volume_out,
+                                void* stream);
+
 /* Measurement utility (bench accounting): re-walks every ray up to its
  * terminationIndex and counts samples and CELL VISITS (a sample whose integer cell differs
  * from the ray's previous one -- the unit the reference's cell cache reloads 8 corners for,

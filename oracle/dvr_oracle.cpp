@@ -95,6 +95,19 @@ struct Scene {
   R fovY, earlyOut;
   int R_, C_;  // tf resolution and channels
 
+  // TF only (preshade_volume): tf_eval / tf_adjoint read tfMode, tf, R_, C_
+  Scene(const DvrTensor& tfT, int mode) {
+    W = H = X = Y = Z = 0;
+    B = 1;
+    filter = camera = blend = 0;
+    tfMode = mode;
+    tf = View<R>(tfT, 3);
+    if (!tf.p) throw std::runtime_error("tf missing");
+    R_ = int(tfT.size[1]);
+    C_ = int(tfT.size[2]);
+    fovY = earlyOut = R(0);
+  }
+
   explicit Scene(const DvrInputs& a) {
     W = a.screen_width;
     H = a.screen_height;
@@ -916,6 +929,7 @@ static void face_distance(const DvrInputs& in, const DvrTensor& termT, const Dvr
 
 }  // namespace dvro
 #include "dvr_oracle_camera.h"
+#include "dvr_oracle_tfutils.h"
 namespace dvro {
 
 template <typename F>
@@ -969,6 +983,15 @@ using namespace dvro;
                                             const DvrTensor* q, const DvrTensor* d,                \
                                             const DvrTensor* go, int32_t reduce, void*) {           \
     return guarded([&] { compare_to_image<R>(*c, *g, *q, *d, *go, reduce); });                      \
+  }                                                                                                 \
+  extern "C" int dvro##P##_preshade_volume(const DvrTensor* v, const DvrTensor* tf, int32_t mode,   \
+                                           const DvrTensor* c, void*) {                             \
+    return guarded([&] { preshade_volume<R>(*v, *tf, mode, *c); });                                 \
+  }                                                                                                 \
+  extern "C" int dvro##P##_preshade_volume_adjoint(const DvrTensor* v, const DvrTensor* tf,         \
+                                                   int32_t mode, const DvrTensor* ac,               \
+                                                   const DvrTensor* av, void*) {                    \
+    return guarded([&] { preshade_volume_adjoint<R>(*v, *tf, mode, *ac, *av); });                   \
   }                                                                                                 \
   extern "C" const char* dvro##P##_last_error() { return g_error.c_str(); }                         \
   extern "C" int dvro##P##_real_size() { return int(sizeof(R)); }

@@ -148,3 +148,75 @@ extern "C" int REFSYM(compare_to_image)(const DvrTensor* colorT, const DvrTensor
     }
   });
 }
+
+// ---- TFUtils::preshadeVolume forward / density adjoint ------------------------------------------------
+// PreshadeVolumeImpl / PreshadeVolumeAdjImpl of renderer/tf_utils_impl.cu:16-33, 98-122 re-assembled from the
+// reference's own TransferFunctionEval<mode>::eval / adjoint<false,false> (renderer/renderer_tf.cuh); that file
+// itself needs cuMat and cannot be compiled here.
+namespace {
+
+template <kernel::TFMode MODE>
+void preshade_impl(const kernel::Tensor4Read& volume, const kernel::Tensor3Read& tf, kernel::Tensor4RW& color) {
+  for (int x = 0; x < volume.size(1); ++x)
+    for (int y = 0; y < volume.size(2); ++y)
+      for (int z = 0; z < volume.size(3); ++z) {
+        real_t density = volume[0][x][y][z];
+        kernel::TransferFunctionEval<MODE> tfEval;
+        real4 c = tfEval.eval(tf, 0, density);
+        color[0][x][y][z] = c.x;
+        color[1][x][y][z] = c.y;
+        color[2][x][y][z] = c.z;
+        color[3][x][y][z] = c.w;
+      }
+}
+
+template <kernel::TFMode MODE>
+void preshade_adj_impl(const kernel::Tensor4Read& volume, const kernel::Tensor3Read& tf,
+                       const kernel::Tensor4Read& adj_color, kernel::Tensor4RW& adj_volume) {
+  DvrTensor none{};
+  kernel::BTensor3RW dummy_adj_tf = make_acc<kernel::BTensor3RW, 3>(none);
+  for (int x = 0; x < volume.size(1); ++x)
+    for (int y = 0; y < volume.size(2); ++y)
+      for (int z = 0; z < volume.size(3); ++z) {
+        real_t density = volume[0][x][y][z];
+        kernel::TransferFunctionEval<MODE> tfEval;
+        real4 adj_c = make_real4(adj_color[0][x][y][z], adj_color[1][x][y][z], adj_color[2][x][y][z],
+                                 adj_color[3][x][y][z]);
+        real_t adj_density = 0;
+        tfEval.template adjoint<false, false>(tf, 0, density, adj_c, adj_density, dummy_adj_tf, nullptr);
+        adj_volume[0][x][y][z] = adj_density;
+      }
+}
+
+}  // namespace
+
+#define TF_SWITCH(mode, CALL)                                                     \
+  switch (mode) {                                                                 \
+    case DVR_TF_IDENTITY: { constexpr auto M = kernel::TFIdentity; CALL; } break;  \
+    case DVR_TF_TEXTURE: { constexpr auto M = kernel::TFTexture; CALL; } break;    \
+    case DVR_TF_LINEAR: { constexpr auto M = kernel::TFLinear; CALL; } break;      \
+    case DVR_TF_GAUSSIAN: { constexpr auto M = kernel::TFGaussian; CALL; } break;  \
+    case DVR_TF_GAUSSIAN_LOG: { constexpr auto M = kernel::TFGaussianLog; CALL; } break; \
+    default: throw std::runtime_error("unknown tf mode");                        \
+  }
+
+extern "C" int REFSYM(preshade_volume)(const DvrTensor* volumeT, const DvrTensor* tfT, int32_t mode,
+                                       const DvrTensor* colorT, void*) {
+  return guarded([&] {
+    auto volume = make_acc<kernel::Tensor4Read, 4>(*volumeT);
+    auto tf = make_acc<kernel::Tensor3Read, 3>(*tfT);
+    auto color = make_acc<kernel::Tensor4RW, 4>(*colorT);
+    TF_SWITCH(mode, preshade_impl<M>(volume, tf, color));
+  });
+}
+
+extern "C" int REFSYM(preshade_volume_adjoint)(const DvrTensor* volumeT, const DvrTensor* tfT, int32_t mode,
+                                               const DvrTensor* adjColorT, const DvrTensor* adjVolumeT, void*) {
+  return guarded([&] {
+    auto volume = make_acc<kernel::Tensor4Read, 4>(*volumeT);
+    auto tf = make_acc<kernel::Tensor3Read, 3>(*tfT);
+    auto adj_color = make_acc<kernel::Tensor4Read, 4>(*adjColorT);
+    auto adj_volume = make_acc<kernel::Tensor4RW, 4>(*adjVolumeT);
+    TF_SWITCH(mode, preshade_adj_impl<M>(volume, tf, adj_color, adj_volume));
+  });
+}

@@ -84,3 +84,35 @@ def run_compare(lib, case, dtype=np.float32, wrap=None, unwrap=None, sync=None):
         sync()
     return dict(difference=unwrap(diff), gradients=unwrap(gout), difference_reduced=unwrap(diff_r),
                 gradients_reduced=unwrap(gout_r))
+
+
+def preshade_cases():
+    """name -> (tf_mode, R, volume shape); TFs from scenes.random_tf"""
+    from diffdvr_b200 import capi
+    return {
+        "preshade_identity": (capi.TF_IDENTITY, 1, (1, 6, 5, 7)),
+        "preshade_texture": (capi.TF_TEXTURE, 8, (1, 9, 6, 8)),
+        "preshade_linear": (capi.TF_LINEAR, 5, (1, 6, 7, 5)),
+        "preshade_gaussian": (capi.TF_GAUSSIAN, 3, (1, 5, 6, 9)),
+        "preshade_gaussianlog": (capi.TF_GAUSSIAN_LOG, 3, (1, 4, 5, 6)),
+    }
+
+
+def run_preshade(lib, case, dtype=np.float32, wrap=None, unwrap=None, sync=None):
+    import scenes
+    wrap = wrap or (lambda a: a)
+    unwrap = unwrap or (lambda t: t)
+    tf_mode, R, shape = case
+    rng = np.random.RandomState(SEED + 2)
+    tf = scenes.random_tf(tf_mode, R, rng, opacity=4.0).astype(dtype)[:1]
+    # densities slightly outside [0, 1] too: clamps of the Identity / Linear TFs
+    volume = rng.uniform(-0.1, 1.1, shape).astype(dtype)
+    adj_color = rng.standard_normal((4,) + shape[1:]).astype(dtype)
+    tv, tt = wrap(volume), wrap(np.ascontiguousarray(tf))
+    color = wrap(np.full((4,) + shape[1:], 7.0, dtype))
+    lib.preshade_volume(tv, tt, tf_mode, color)
+    adj_volume = wrap(np.full(shape, 7.0, dtype))
+    lib.preshade_volume_adjoint(tv, tt, tf_mode, wrap(adj_color), adj_volume)
+    if sync:
+        sync()
+    return dict(tf=tf, volume=volume, adj_color=adj_color, color=unwrap(color), adj_volume=unwrap(adj_volume))

@@ -53,6 +53,12 @@ def main():
         if not os.path.exists(path) or "--all" in sys.argv:
             np.savez_compressed(path, **camera_cases.run_compare(ref, case))
             print(name)
+    for name, case in camera_cases.preshade_cases().items():
+        path = os.path.join(HERE, f"ref_{name}.npz")
+        if not os.path.exists(path) or "--all" in sys.argv:
+            out = camera_cases.run_preshade(ref, case)
+            np.savez_compressed(path, **{k: out[k] for k in ("tf", "color", "adj_volume")})
+            print(name)
     src = "/root/reference/unittests/NonConvexDensity.tsv"
     if os.path.exists(src):
         shutil.copyfile(src, os.path.join(HERE, "NonConvexDensity.tsv"))
