@@ -13,6 +13,7 @@
 #include "../../../include/dvr_b200.h"
 #include "renderer.h"
 #include "camera.h"
+#include "tf_utils.h"
 
 namespace py = pybind11;
 using namespace renderer;
@@ -269,6 +270,27 @@ PYBIND11_MODULE(pyrenderer, m) {
                   py::doc("Viewport matrix for generate_rays() from a position on the sphere around a center."),
                   py::arg("center"), py::arg("yaw_radians"), py::arg("pitch_radians"), py::arg("distance"),
                   py::arg("orientation"));
+
+  // ---- transfer-function utilities (bindings.cpp:560-571) -----------------------------------------
+  py::class_<TFPoint>(m, "TFPoint")
+      .def(py::init<>())
+      .def(py::init([](real_t pos, real4 val) { return TFPoint{pos, val}; }))
+      .def_readwrite("pos", &TFPoint::pos)
+      .def_readwrite("val", &TFPoint::val);
+
+  py::class_<TFUtils>(m, "TFUtils")
+      .def_static("assemble_from_settings", &TFUtils::assembleFromSettings, py::arg("color_values_lab"),
+                  py::arg("color_positions"), py::arg("opacity_values"), py::arg("opacity_positions"),
+                  py::arg("min_density"), py::arg("max_density"), py::arg("opacity_scaling"),
+                  py::arg("purge_zero_opacity_regions") = true)
+      .def_static("get_piecewise_tensor", &TFUtils::getPiecewiseTensor)
+      .def_static("get_texture_tensor", &TFUtils::getTextureTensor)
+      .def_static("preshade_volume", &TFUtils::preshadeVolume,
+                  py::doc("Pre-shades a density volume 1*X*Y*Z with the TF into a colour volume 4*X*Y*Z "
+                          "(r, g, b, opacity). Differentiable with respect to the density."),
+                  py::arg("density"), py::arg("tf"), py::arg("tfMode"));
+  m.def("lab_to_rgb", &labToRgb);
+  m.def("rgb_to_lab", &rgbToLab);
 
   // ---- timing (bindings.cpp:554-558) ------------------------------------------------------------
   py::class_<GPUTimer>(m, "GpuTimer")

@@ -208,3 +208,40 @@ def test_compare_to_image_through_host_layer():
     assert scenes.rel_l2(gr_.cpu().numpy(), want["gradients_reduced"]) <= 1e-4
     with pytest.raises(RuntimeError):  # wrong output shape for the reduced variant
         pyr.Renderer.compare_to_image(color, grads, reference, diff, gout, True)
+
+
+def test_preshade_volume_autograd_and_preshaded_render():
+    """TFUtils.preshade_volume: values and density gradient against the oracle; the result feeds the pre-shaded
+    marcher (train_volume.py --preshaded pipeline)."""
+    import camera_cases as cc
+    import oracle_loader as ol
+    case = cc.preshade_cases()["preshade_gaussian"]
+    want = cc.run_preshade(ol.port(32), case)
+    density = torch.from_numpy(want["volume"]).cuda().requires_grad_(True)
+    tf = torch.from_numpy(np.ascontiguousarray(want["tf"])).cuda()
+    color = pyr.TFUtils.preshade_volume(density, tf, pyr.TFMode.Gaussian)
+    assert color.shape == (4,) + density.shape[1:]
+    assert scenes.rel_l2(color.detach().cpu().numpy(), want["color"]) <= 1e-5
+    (color * torch.from_numpy(want["adj_color"]).cuda()).sum().backward()
+    assert scenes.rel_l2(density.grad.cpu().numpy(), want["adj_volume"]) <= 1e-4
+    # pre-shaded render of the colour volume
+    i = pyr.RendererInputs()
+    i.screen_size = pyr.int2(32, 24)
+    i.volume_filter_mode = pyr.VolumeFilterMode.Preshaded
+    i.volume = color.detach()
+    i.box_min = pyr.real3(-0.5, -0.5, -0.5)
+    i.box_size = pyr.real3(1, 1, 1)
+    i.camera_mode = pyr.CameraMode.ReferenceFrame
+    vp = pyr.Camera.viewport_from_sphere(torch.zeros(1, 3, device="cuda"), torch.tensor([[0.5]], device="cuda"),
+                                         torch.tensor([[0.3]], device="cuda"), torch.tensor([[1.8]], device="cuda"),
+                                         pyr.Orientation.Ym)
+    i.camera = pyr.CameraReferenceFrame(vp, 0.6)
+    i.step_size = 0.02
+    i.tf_mode = pyr.TFMode.Preshaded
+    i.tf = tf
+    i.blend_mode = pyr.BlendMode.BeerLambert
+    out = pyr.RendererOutputs(torch.empty(1, 24, 32, 4, device="cuda"),
+                              torch.empty(1, 24, 32, dtype=torch.int32, device="cuda"))
+    pyr.Renderer.render_forward(i, out)
+    pyr.sync()
+    assert torch.isfinite(out.color).all() and out.color[..., 3].max().item() > 0.05

@@ -194,3 +194,72 @@ def test_generate_rays_rejects_cpu_tensors():
     with pytest.raises(RuntimeError, match="no CPU back-end"):
         pyr.Renderer.compare_to_image(torch.zeros(1, 2, 2, 4), torch.zeros(1, 2, 2, 1, 4), torch.zeros(1, 2, 2, 4),
                                       torch.zeros(1, 2, 2, 1), torch.zeros(1, 2, 2, 1), False)
+
+
+# ---- TFUtils (bindings/bindings.cpp:560-571) --------------------------------------------------------------
+def test_lab_rgb_round_trip_and_known_values():
+    # D65 white: Lab (100, 0, 0) <-> rgb (1, 1, 1); mid grey rgb 0.5 -> L* = 53.39
+    w = pyr.lab_to_rgb(pyr.real3(100.0, 0.0, 0.0))
+    assert np.allclose([w.x, w.y, w.z], 1.0, atol=2e-3)
+    g = pyr.rgb_to_lab(pyr.real3(0.5, 0.5, 0.5))
+    assert abs(g.x - 53.389) < 0.02 and abs(g.y) < 0.05 and abs(g.z) < 0.05
+    rng = np.random.RandomState(0)
+    for rgb in rng.uniform(0.05, 0.95, (20, 3)):
+        lab = pyr.rgb_to_lab(pyr.real3(*[float(v) for v in rgb]))
+        back = pyr.lab_to_rgb(lab)
+        assert np.allclose([back.x, back.y, back.z], rgb, atol=2e-4)
+
+
+def _assemble(colors_lab, cpos, opac, opos, lo=0.0, hi=1.0, scale=10.0, purge=False):
+    pts = pyr.TFUtils.assemble_from_settings([pyr.real3(*[float(v) for v in c]) for c in colors_lab],
+                                             [float(v) for v in cpos], [float(v) for v in opac],
+                                             [float(v) for v in opos], lo, hi, scale, purge)
+    return pts
+
+
+def test_assemble_from_settings_interpolates_both_lists():
+    colors = np.array([[30.0, 20.0, -40.0], [70.0, -30.0, 50.0], [90.0, 5.0, 5.0]])
+    cpos, opac, opos = [0.1, 0.5, 0.9], [0.0, 0.8, 0.2, 0.6], [0.05, 0.3, 0.6, 0.95]
+    pts = _assemble(colors, cpos, opac, opos, scale=10.0)
+    pos = np.array([p.pos for p in pts])
+    assert np.all(np.diff(pos) >= 0) and pos[0] == -1.0           # sorted, guard point at -1
+    assert set(np.round(pos, 6)) >= set(np.round(cpos + opos, 6))  # every control point of either list
+    cg, og = [-1.0] + cpos + [2.0], [-1.0] + opos + [2.0]
+    lab_g = np.vstack([colors[:1], colors, colors[-1:]])
+    op_g = [opac[0]] + opac + [opac[-1]]
+    for p in pts:
+        want_a = np.clip(np.interp(p.pos, og, op_g), 0, 1 - 1.2e-7) * 10.0
+        assert abs(p.val.w - want_a) < 1e-5
+        lab = [np.interp(p.pos, cg, lab_g[:, k]) for k in range(3)]
+        rgb = pyr.lab_to_rgb(pyr.real3(*[float(v) for v in lab]))
+        want = np.clip([rgb.x, rgb.y, rgb.z], 0, 1 - 1.2e-7)
+        assert np.allclose([p.val.x, p.val.y, p.val.z], want, atol=1e-5)
+
+
+def test_assemble_maps_density_range_and_purges_zero_opacity():
+    colors = np.array([[50.0, 0.0, 0.0], [60.0, 10.0, 10.0]])
+    pts = _assemble(colors, [0.0, 1.0], [1.0, 1.0], [0.0, 1.0], lo=0.2, hi=0.6, scale=1.0)
+    pos = sorted(p.pos for p in pts)
+    assert any(abs(v - 0.2) < 1e-6 for v in pos) and any(abs(v - 0.6) < 1e-6 for v in pos)
+    # a long zero-opacity stretch with several colour points inside: purge drops the interior ones
+    cpos = [0.1, 0.2, 0.3, 0.4, 0.9]
+    cols = np.tile(np.array([[50.0, 0.0, 0.0]]), (5, 1))
+    keep = _assemble(cols, cpos, [0.0, 0.0, 1.0], [0.0, 0.5, 1.0], purge=False)
+    purged = _assemble(cols, cpos, [0.0, 0.0, 1.0], [0.0, 0.5, 1.0], purge=True)
+    assert len(purged) < len(keep)
+
+
+def test_piecewise_and_texture_tensors():
+    pts = [pyr.TFPoint(-1.0, pyr.real4(0.1, 0.2, 0.3, 0.0)), pyr.TFPoint(0.25, pyr.real4(0.1, 0.2, 0.3, 0.0)),
+           pyr.TFPoint(0.75, pyr.real4(0.9, 0.6, 0.3, 8.0)), pyr.TFPoint(2.0, pyr.real4(0.9, 0.6, 0.3, 8.0))]
+    lin = pyr.TFUtils.get_piecewise_tensor(pts)
+    assert lin.shape == (1, 4, 5) and lin.dtype == torch.float32 and not lin.is_cuda
+    assert np.allclose(lin[0, :, 4].numpy(), [-1, 0.25, 0.75, 2]) and np.allclose(lin[0, 2, :4].numpy(), [0.9, 0.6, 0.3, 8])
+    tex = pyr.TFUtils.get_texture_tensor(pts, 16)
+    assert tex.shape == (1, 16, 4)
+    dens = (np.arange(16) + 0.5) / 16
+    want_a = np.interp(dens, [-1, 0.25, 0.75, 2], [0, 0, 8, 8])
+    assert np.allclose(tex[0, :, 3].numpy(), want_a, atol=1e-5)
+    assert np.allclose(tex[0, :, 0].numpy(), np.interp(dens, [-1, 0.25, 0.75, 2], [0.1, 0.1, 0.9, 0.9]), atol=1e-6)
+    with pytest.raises(RuntimeError, match="no CPU back-end"):
+        pyr.TFUtils.preshade_volume(torch.zeros(1, 2, 2, 2), tex, pyr.TFMode.Texture)
