@@ -243,12 +243,19 @@ class Library:
         self._sig("preshade_volume", [P(DvrTensor), P(DvrTensor), ctypes.c_int32, P(DvrTensor), ctypes.c_void_p])
         self._sig("preshade_volume_adjoint", [P(DvrTensor), P(DvrTensor), ctypes.c_int32, P(DvrTensor), P(DvrTensor),
                                               ctypes.c_void_p])
+        # renderer::Volume producers (row f3); the reference-built shim of the marcher does not export them
+        self._sig("create_implicit_volume", [ctypes.c_int32, P(ctypes.c_float), P(DvrTensor), ctypes.c_void_p], True)
+        self._sig("volume_from_raw", [ctypes.c_void_p, ctypes.c_int32, P(DvrTensor), ctypes.c_void_p], True)
+        self._sig("volume_to_raw", [P(DvrTensor), ctypes.c_void_p, ctypes.c_void_p], True)
+        self._sig("downsample_volume", [P(DvrTensor), P(DvrTensor), ctypes.c_void_p], True)
         f = getattr(self.lib, prefix + "last_error")
         f.restype = ctypes.c_char_p
         f.argtypes = []
 
-    def _sig(self, name, argtypes):
-        f = getattr(self.lib, self.prefix + name)
+    def _sig(self, name, argtypes, optional=False):
+        f = getattr(self.lib, self.prefix + name, None) if optional else getattr(self.lib, self.prefix + name)
+        if f is None:
+            return
         f.restype = ctypes.c_int
         f.argtypes = argtypes
 
@@ -314,6 +321,29 @@ class Library:
         self._check(getattr(self.lib, self.prefix + "preshade_volume_adjoint")(
             tensor_view(density_volume), tensor_view(tf), int(tf_mode), tensor_view(adj_color),
             tensor_view(adj_volume_out), stream))
+
+    # -- renderer::Volume producers -----------------------------------------------------------------
+    def create_implicit_volume(self, equation, volume_out, params=None, stream: int = 0):
+        """volume_out 1*n*n*n (written); params = (fM, alpha, scale, a) or None for the reference's defaults."""
+        p = (ctypes.c_float * 4)(*[float(v) for v in params]) if params is not None else None
+        self._check(getattr(self.lib, self.prefix + "create_implicit_volume")(
+            int(equation), p, tensor_view(volume_out), stream))
+
+    def volume_from_raw(self, raw, dtype, volume_out, stream: int = 0):
+        """raw: flat u8 / u16 / f32 array or tensor of X*Y*Z elements, X fastest (.cvol body); dtype 0 / 1 / 2."""
+        self._check(getattr(self.lib, self.prefix + "volume_from_raw")(
+            _data_ptr(raw), int(dtype), tensor_view(volume_out), stream))
+
+    def volume_to_raw(self, volume, raw_out, stream: int = 0):
+        self._check(getattr(self.lib, self.prefix + "volume_to_raw")(tensor_view(volume), _data_ptr(raw_out), stream))
+
+    def downsample_volume(self, volume, volume_out, stream: int = 0):
+        self._check(getattr(self.lib, self.prefix + "downsample_volume")(
+            tensor_view(volume), tensor_view(volume_out), stream))
+
+
+def _data_ptr(a):
+    return a.data_ptr() if hasattr(a, "data_ptr") else a.ctypes.data
 
 
 _PRODUCT: Optional["ProductLibrary"] = None

@@ -831,6 +831,85 @@ int dvr_preshade_volume_adjoint(const DvrTensor* vol, const DvrTensor* tf, int32
   });
 }
 
+// ---- renderer::Volume on the device --------------------------------------------
+namespace {
+void volume_dims(const DvrTensor& t, const char* name, int& X, int& Y, int& Z) {
+  check_dim(t, name, 4);
+  check_size(t, name, 0, 1);
+  for (int d = 1; d < 4; ++d)
+    if (t.size[d] <= 0) fail(DVR_ERR_INVALID_ARGUMENT, "%s must not be empty", name);
+  if (t.size[1] * t.size[2] * t.size[3] > 0x7fffffffll)  // renderer/volume.cpp:192-193
+    fail(DVR_ERR_INVALID_ARGUMENT, "Dataset is too big, must fit into an 32-bit signed int");
+  X = int(t.size[1]); Y = int(t.size[2]); Z = int(t.size[3]);
+}
+}  // namespace
+
+int dvr_create_implicit_volume(int32_t equation, const float* params, const DvrTensor* volume_out, void* stream) {
+  return guarded([&] {
+    if (!volume_out) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (equation < 0 || equation >= kEqCount) fail(DVR_ERR_INVALID_ARGUMENT, "unknown implicit equation %d", equation);
+    ImplicitArgs a{};
+    volume_dims(*volume_out, "volume", a.X, a.Y, a.Z);
+    if (a.X != a.Y || a.Y != a.Z) fail(DVR_ERR_INVALID_ARGUMENT, "implicit volumes are cubes: X == Y == Z expected");
+    // sampling box per equation (boxMin / boxMax members, renderer/volume_implicit.cpp:30-215)
+    static const float kBox[kEqCount] = {1, 1, 1, 1, 2, 2, 1.5f, 1, 5, 1, 0.5f, 1, 2, 2, 1};
+    a.equation = equation;
+    a.boxMin = -kBox[equation];
+    a.scaleStep = (kBox[equation] - a.boxMin) / float(a.X - 1);  // renderer/volume.cpp:375
+    a.fM = params ? params[0] : 6.0f;
+    a.alpha = params ? params[1] : 0.25f;
+    a.scale = params ? params[2] : 0.5f;
+    a.a = params ? params[3] : 0.25f;
+    a.out = static_cast<float*>(volume_out->ptr);
+    a.sx = volume_out->stride[1]; a.sy = volume_out->stride[2]; a.sz = volume_out->stride[3];
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    after_launch(launch_implicit_volume(a, s), "dvr_create_implicit_volume", s);
+  });
+}
+
+int dvr_volume_from_raw(const void* raw, int32_t dtype, const DvrTensor* volume_out, void* stream) {
+  return guarded([&] {
+    if (!raw || !volume_out) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    if (dtype < 0 || dtype > 2) fail(DVR_ERR_INVALID_ARGUMENT, "unknown .cvol data type %d", dtype);
+    RawVolumeArgs a{};
+    volume_dims(*volume_out, "volume", a.X, a.Y, a.Z);
+    a.raw = const_cast<void*>(raw);
+    a.vol = static_cast<float*>(volume_out->ptr);
+    a.sx = volume_out->stride[1]; a.sy = volume_out->stride[2]; a.sz = volume_out->stride[3];
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    after_launch(launch_volume_raw(dtype, false, a, s), "dvr_volume_from_raw", s);
+  });
+}
+
+int dvr_volume_to_raw(const DvrTensor* volume, float* raw_out, void* stream) {
+  return guarded([&] {
+    if (!raw_out || !volume) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    RawVolumeArgs a{};
+    volume_dims(*volume, "volume", a.X, a.Y, a.Z);
+    a.raw = raw_out;
+    a.vol = static_cast<float*>(volume->ptr);
+    a.sx = volume->stride[1]; a.sy = volume->stride[2]; a.sz = volume->stride[3];
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    after_launch(launch_volume_raw(2, true, a, s), "dvr_volume_to_raw", s);
+  });
+}
+
+int dvr_downsample_volume(const DvrTensor* volume, const DvrTensor* volume_out, void* stream) {
+  return guarded([&] {
+    if (!volume || !volume_out) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    DownsampleArgs a{};
+    volume_dims(*volume, "volume", a.X, a.Y, a.Z);
+    volume_dims(*volume_out, "mipmap level", a.oX, a.oY, a.oZ);
+    if (a.oX > a.X || a.oY > a.Y || a.oZ > a.Z) fail(DVR_ERR_INVALID_ARGUMENT, "a mipmap level cannot be larger than the volume");
+    a.in = static_cast<const float*>(volume->ptr);
+    a.sx = volume->stride[1]; a.sy = volume->stride[2]; a.sz = volume->stride[3];
+    a.out = static_cast<float*>(volume_out->ptr);
+    a.ox = volume_out->stride[1]; a.oy = volume_out->stride[2]; a.oz = volume_out->stride[3];
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    after_launch(launch_downsample_volume(a, s), "dvr_downsample_volume", s);
+  });
+}
+
 int dvr_count_cell_visits(const DvrInputs* inputs, const DvrTensor* termination_index, uint64_t* counts,
                           void* stream) {
   return guarded([&] {

@@ -48,6 +48,11 @@ cudaError_t launch_compare_to_image(const CompareArgs& a, cudaStream_t stream); 
 cudaError_t launch_preshade(int tf, bool adjoint, const RayInputs& in, const PreshadeArgs& a, size_t smem,
                             cudaStream_t stream);
 
+// renderer::Volume on the device (dvr_volume.cu)
+cudaError_t launch_implicit_volume(const ImplicitArgs& a, cudaStream_t stream);
+cudaError_t launch_volume_raw(int dtype, bool toRaw, const RawVolumeArgs& a, cudaStream_t stream);
+cudaError_t launch_downsample_volume(const DownsampleArgs& a, cudaStream_t stream);
+
 // per-(tf, blend) translation units (parallel compilation)
 #define DVR_DECL_ADJ(TF, BL)                                                                          \
   cudaError_t launch_adjoint_##TF##_##BL(int filter, bool hasVol, int tfacc, bool hasRay,             \

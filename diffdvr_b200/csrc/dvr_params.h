@@ -159,4 +159,38 @@ struct PreshadeArgs {
   long long ax, ay, az;
 };
 
+// Volume::ImplicitEquation (renderer/volume.h:163-181)
+enum : int {
+  kEqMarschnerLobb = 0, kEqCube, kEqSphere, kEqInverseSphere, kEqDingDong, kEqEndrass, kEqBarth, kEqHeart, kEqKleine,
+  kEqCassini, kEqSteiner, kEqCrossCap, kEqKummer, kEqBlobby, kEqTube, kEqCount
+};
+
+// Volume::createImplicitDataset (renderer/volume_implicit.cpp:224-256 -> volume.cpp:369-387)
+struct ImplicitArgs {
+  int equation;
+  int X, Y, Z;
+  float boxMin, scaleStep;           // position = boxMin + index * scaleStep
+  float fM, alpha, scale, a;         // MarschnerLobb "fM", "alpha"; Cube "scale"; Cassini "a"
+  float* out;
+  long long sx, sy, sz;
+};
+
+// .cvol body (X fastest; u8 | u16 | f32) <-> the fp32 density tensor (renderer/volume.cpp:86-151, 232-276)
+struct RawVolumeArgs {
+  void* raw;
+  int X, Y, Z;
+  float* vol;
+  long long sx, sy, sz;
+};
+
+// Volume::createMipmapLevel (renderer/volume.cpp:359-365)
+struct DownsampleArgs {
+  const float* in;
+  int X, Y, Z;
+  long long sx, sy, sz;
+  float* out;
+  int oX, oY, oZ;
+  long long ox, oy, oz;
+};
+
 }  // namespace dvr

@@ -8,12 +8,14 @@
 #include <torch/extension.h>
 
 #include <cstdio>
+#include <sstream>
 #include <stdexcept>
 
 #include "../../../include/dvr_b200.h"
 #include "renderer.h"
 #include "camera.h"
 #include "tf_utils.h"
+#include "volume.h"
 
 namespace py = pybind11;
 using namespace renderer;
@@ -291,6 +293,75 @@ PYBIND11_MODULE(pyrenderer, m) {
                   py::arg("density"), py::arg("tf"), py::arg("tfMode"));
   m.def("lab_to_rgb", &labToRgb);
   m.def("rgb_to_lab", &rgbToLab);
+
+  // ---- volumes (bindings.cpp:234-304) ------------------------------------------------------------
+  py::enum_<Volume::ImplicitEquation>(m, "ImplicitEquation")
+      .value("MarschnerLobb", Volume::ImplicitEquation::MARSCHNER_LOBB)
+      .value("Cube", Volume::ImplicitEquation::CUBE)
+      .value("Sphere", Volume::ImplicitEquation::SPHERE)
+      .value("InverseSphere", Volume::ImplicitEquation::INVERSE_SPHERE)
+      .value("DingDong", Volume::ImplicitEquation::DING_DONG)
+      .value("Endrass", Volume::ImplicitEquation::ENDRASS)
+      .value("Barth", Volume::ImplicitEquation::BARTH)
+      .value("Heart", Volume::ImplicitEquation::HEART)
+      .value("Kleine", Volume::ImplicitEquation::KLEINE)
+      .value("Cassini", Volume::ImplicitEquation::CASSINI)
+      .value("Steiner", Volume::ImplicitEquation::STEINER)
+      .value("CrossCap", Volume::ImplicitEquation::CROSS_CAP)
+      .value("Kummer", Volume::ImplicitEquation::KUMMER)
+      .value("Blobbly", Volume::ImplicitEquation::BLOBBY)  // sic, bindings.cpp:248
+      .value("Tube", Volume::ImplicitEquation::TUBE);
+  py::class_<Volume, std::shared_ptr<Volume>>(m, "Volume")
+      .def(py::init<std::string>())
+      .def("create_mipmap_level", &Volume::createMipmapLevel)
+      .def_property_readonly("world_size",
+                             [](const Volume& v) { return make_real3(v.worldSizeX(), v.worldSizeY(), v.worldSizeZ()); })
+      .def("set_world_size", [](Volume& v, float x, float y, float z) { v.setWorldSize(x, y, z); })
+      .def_property_readonly("resolution", &Volume::baseResolution)
+      .def_static("create_implicit",
+                  [](Volume::ImplicitEquation name, int resolution, py::kwargs kwargs) {
+                    std::unordered_map<std::string, float> args;
+                    for (const auto& e : kwargs) args.insert({e.first.cast<std::string>(), e.second.cast<float>()});
+                    return Volume::createImplicitDataset(resolution, name, args);
+                  })
+      .def_static("from_numpy",
+                  [](py::buffer b) {
+                    const py::buffer_info info = b.request();
+                    if (info.format != py::format_descriptor<real_t>::format())
+                      throw std::runtime_error("Incompatible format: expected a real array!");
+                    if (info.ndim != 3) throw std::runtime_error("Incompatible buffer dimension, expected 3!");
+                    const long long sizes[] = {info.shape[0], info.shape[1], info.shape[2]};
+                    const long long strides[] = {(long long)(info.strides[0] / ssize_t(sizeof(real_t))),
+                                                 (long long)(info.strides[1] / ssize_t(sizeof(real_t))),
+                                                 (long long)(info.strides[2] / ssize_t(sizeof(real_t)))};
+                    return Volume::createFromBuffer(static_cast<const real_t*>(info.ptr), sizes, strides);
+                  },
+                  py::doc("Create a volume from a 3D numpy array of type 'real'"))
+      .def_static("from_tensor", &Volume::createFromTensor,
+                  py::doc("Wrap a float tensor of shape X*Y*Z or 1*X*Y*Z (a CUDA tensor is not copied)"))
+      .def("copy_to_gpu", [](const Volume& v) { v.copyCpuToGpu(); },
+           py::doc("No-op: the device copy is the primary one here"))
+      .def("save", [](const Volume& v, const std::string& filename, int compression) { v.save(filename, compression); },
+           py::arg("filename"), py::arg("compression") = 0)
+      .def("getDataCpu", &Volume::dataCpu,
+           py::doc("Returns the density tensor of shape 1*X*Y*Z for the specified layer with the data located on the CPU"),
+           py::arg("level"))
+      .def("getDataGpu", &Volume::dataGpu,
+           py::doc("Returns the density tensor of shape 1*X*Y*Z for the specified layer with the data located on the GPU"),
+           py::arg("level"));
+
+  // the .cvol body codec on its own (host code; lets the CPU test-suite pin it against the reference's LZ4)
+  m.def("cvol_compress_body", [](py::bytes data, int level) {
+    const std::string in = data;
+    const std::vector<uint8_t> out = cvol::compressBody(reinterpret_cast<const uint8_t*>(in.data()), in.size(), level);
+    return py::bytes(reinterpret_cast<const char*>(out.data()), out.size());
+  }, py::arg("data"), py::arg("level"));
+  m.def("cvol_decompress_body", [](py::bytes data, size_t size) {
+    std::istringstream in{std::string(data)};
+    std::string out(size, '\0');
+    cvol::decompressBody(in, reinterpret_cast<uint8_t*>(&out[0]), size, "buffer");
+    return py::bytes(out);
+  }, py::arg("data"), py::arg("size"));
 
   // ---- timing (bindings.cpp:554-558) ------------------------------------------------------------
   py::class_<GPUTimer>(m, "GpuTimer")

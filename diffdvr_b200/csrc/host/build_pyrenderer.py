@@ -27,8 +27,9 @@ def main():
     if not os.path.exists(lib):
         raise SystemExit(f"{lib} missing: build the CUDA library first (make -C diffdvr_b200/csrc)")
     srcs = [os.path.join(HERE, "renderer.cpp"), os.path.join(HERE, "camera.cpp"), os.path.join(HERE, "tf_utils.cpp"),
-            os.path.join(HERE, "bindings.cpp")]
-    deps = srcs + [os.path.join(HERE, "renderer.h"), os.path.join(HERE, "camera.h"), os.path.join(HERE, "tf_utils.h"), os.path.join(PKG, "..", "include", "dvr_b200.h"), lib, __file__]
+            os.path.join(HERE, "volume.cpp"), os.path.join(HERE, "lz4_block.cpp"), os.path.join(HERE, "bindings.cpp")]
+    deps = srcs + [os.path.join(HERE, "renderer.h"), os.path.join(HERE, "camera.h"), os.path.join(HERE, "tf_utils.h"),
+                   os.path.join(HERE, "volume.h"), os.path.join(HERE, "lz4_block.h"), os.path.join(PKG, "..", "include", "dvr_b200.h"), lib, __file__]
     if os.path.exists(out) and all(os.path.getmtime(out) >= os.path.getmtime(d) for d in deps):
         print("pyrenderer is up to date")
         return
@@ -43,7 +44,7 @@ def main():
         print("+", " ".join(cmd), flush=True)
         subprocess.run(cmd, check=True)
 
-    with ThreadPoolExecutor(4) as ex:
+    with ThreadPoolExecutor(6) as ex:
         list(ex.map(compile_one, zip(srcs, objs)))
     tlib = os.path.join(os.path.dirname(torch.__file__), "lib")
     link = [cxx, "-shared", "-o", out] + objs + [f"-L{tlib}", "-lc10", "-lc10_cuda", "-ltorch_cpu", "-ltorch",

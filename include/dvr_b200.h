@@ -215,6 +215,34 @@ DVR_API int dvr_preshade_volume_adjoint(const DvrTensor* density_volume, const D
                                 const DvrTensor* adj_color, const DvrTensor* adj_volume_out,
                                 void* stream);
 
+/* ---- renderer::Volume on the device ---------------------------------- */
+
+/* Volume::ImplicitEquation (renderer/volume.h:163-181) */
+enum DvrImplicitEquation {
+  DVR_EQ_MARSCHNER_LOBB = 0, DVR_EQ_CUBE = 1, DVR_EQ_SPHERE = 2, DVR_EQ_INVERSE_SPHERE = 3, DVR_EQ_DING_DONG = 4,
+  DVR_EQ_ENDRASS = 5, DVR_EQ_BARTH = 6, DVR_EQ_HEART = 7, DVR_EQ_KLEINE = 8, DVR_EQ_CASSINI = 9, DVR_EQ_STEINER = 10,
+  DVR_EQ_CROSS_CAP = 11, DVR_EQ_KUMMER = 12, DVR_EQ_BLOBBY = 13, DVR_EQ_TUBE = 14
+};
+
+/* Volume::createImplicitDataset (renderer/volume_implicit.cpp:224-256 over Volume::createSyntheticDataset,
+ * renderer/volume.cpp:369-387): volume_out[0][x][y][z] = f(boxMin + (x, y, z) * (boxMax - boxMin) / (n - 1)),
+ * volume_out 1*n*n*n, any strides. params: HOST pointer to 4 floats {"fM", "alpha" (MarschnerLobb), "scale" (Cube),
+ * "a" (Cassini)}; NULL = the reference's defaults {6, 0.25, 0.5, 0.25}. */
+DVR_API int dvr_create_implicit_volume(int32_t equation, const float* params, const DvrTensor* volume_out,
+                                       void* stream);
+
+/* The conversion step of Volume::Volume(filename) (renderer/volume.cpp:232-276): `raw` = DEVICE pointer to the
+ * decompressed .cvol body, X*Y*Z elements with X FASTEST, dtype 0 = u8 (/255), 1 = u16 (/65535), 2 = f32;
+ * volume_out 1*X*Y*Z fp32, any strides. */
+DVR_API int dvr_volume_from_raw(const void* raw, int32_t dtype, const DvrTensor* volume_out, void* stream);
+
+/* The inverse, for Volume::save (renderer/volume.cpp:86-151): raw_out = DEVICE pointer to X*Y*Z floats, X fastest. */
+DVR_API int dvr_volume_to_raw(const DvrTensor* volume, float* raw_out, void* stream);
+
+/* Volume::createMipmapLevel (renderer/volume.cpp:359-365, at::adaptive_avg_pool3d): volume 1*X*Y*Z ->
+ * volume_out 1*oX*oY*oZ, cell o averaging the input range [floor(o*I/O), ceil((o+1)*I/O)) per axis. */
+DVR_API int dvr_downsample_volume(const DvrTensor* volume, const DvrTensor* volume_out, void* stream);
+
 /* Measurement utility (bench accounting): re-walks every ray up to its
  * terminationIndex and counts samples and CELL VISITS (a sample whose integer cell differs
  * from the ray's previous one -- the unit the reference's cell cache reloads 8 corners for,

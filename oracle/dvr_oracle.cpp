@@ -930,6 +930,7 @@ static void face_distance(const DvrInputs& in, const DvrTensor& termT, const Dvr
 }  // namespace dvro
 #include "dvr_oracle_camera.h"
 #include "dvr_oracle_tfutils.h"
+#include "dvr_oracle_volume.h"
 namespace dvro {
 
 template <typename F>
@@ -992,6 +993,20 @@ using namespace dvro;
                                                    int32_t mode, const DvrTensor* ac,               \
                                                    const DvrTensor* av, void*) {                    \
     return guarded([&] { preshade_volume_adjoint<R>(*v, *tf, mode, *ac, *av); });                   \
+  }                                                                                                 \
+  extern "C" int dvro##P##_create_implicit_volume(int32_t eq, const float* params,                  \
+                                                  const DvrTensor* v, void*) {                      \
+    return guarded([&] { create_implicit_volume<R>(eq, params, *v); });                             \
+  }                                                                                                 \
+  extern "C" int dvro##P##_volume_from_raw(const void* raw, int32_t dtype, const DvrTensor* v,      \
+                                           void*) {                                                 \
+    return guarded([&] { volume_from_raw<R>(raw, dtype, *v); });                                    \
+  }                                                                                                 \
+  extern "C" int dvro##P##_volume_to_raw(const DvrTensor* v, float* raw, void*) {                   \
+    return guarded([&] { volume_to_raw<R>(*v, raw); });                                             \
+  }                                                                                                 \
+  extern "C" int dvro##P##_downsample_volume(const DvrTensor* v, const DvrTensor* o, void*) {       \
+    return guarded([&] { downsample_volume<R>(*v, *o); });                                          \
   }                                                                                                 \
   extern "C" const char* dvro##P##_last_error() { return g_error.c_str(); }                         \
   extern "C" int dvro##P##_real_size() { return int(sizeof(R)); }

@@ -14,6 +14,10 @@ Run in the build container (needs /root/reference and `make -C oracle ref`):
 * ``ref_camera_*.npz``: Camera::generateRays (forward + backward) and Renderer::compareToImage from the
   same library (oracle/ref_shim_camera.cpp: the reference's CameraEval / adjNormalize / adjCross /
   CompareToImage headers) on the seeded inputs of tests/camera_cases.py.
+* ``ref_volume_implicit.npz``: Volume::createImplicitDataset of the reference's own volume_implicit.cpp / volume.cpp
+  (oracle/_ref/libdvr_refvol.so, compiled unmodified; oracle/ref_shim_volume.cpp) on the cases of
+  tests/volume_cases.py; ``ref_volume_c{0,1,9}.cvol``: one seeded 20 x 13 x 9 volume written by the reference's
+  Volume::save uncompressed, with LZ4 fast and with LZ4 HC level 9 (its vendored liblz4).
 * ``NonConvexDensity.tsv``: copied verbatim from /root/reference/unittests/NonConvexDensity.tsv
   (the reference's committed known-answer table, generator unittests/testNonConvexDensity.cpp:8-80).
 """
@@ -30,6 +34,7 @@ import camera_cases  # noqa: E402
 import golden_cases  # noqa: E402
 import oracle_loader as ol  # noqa: E402
 import scenes  # noqa: E402
+import volume_cases  # noqa: E402
 
 
 def main():
@@ -59,6 +64,18 @@ def main():
             out = camera_cases.run_preshade(ref, case)
             np.savez_compressed(path, **{k: out[k] for k in ("tf", "color", "adj_volume")})
             print(name)
+    rv = ol.refvol()
+    assert rv is not None, "oracle/_ref/libdvr_refvol.so missing: run `make -C oracle refvol`"
+    path = os.path.join(HERE, "ref_volume_implicit.npz")
+    if not os.path.exists(path) or "--all" in sys.argv:
+        np.savez_compressed(path, **{name: rv.create_implicit(eq, n, **params)
+                                     for name, (eq, n, params) in volume_cases.implicit_cases().items()})
+        print("ref_volume_implicit")
+    for comp in (0, 1, 9):
+        path = os.path.join(HERE, f"ref_volume_c{comp}.cvol")
+        if not os.path.exists(path) or "--all" in sys.argv:
+            rv.save(path, volume_cases.golden_cvol_volume(), volume_cases.GOLDEN_CVOL_WORLD, comp)
+            print(os.path.basename(path), os.path.getsize(path))
     src = "/root/reference/unittests/NonConvexDensity.tsv"
     if os.path.exists(src):
         shutil.copyfile(src, os.path.join(HERE, "NonConvexDensity.tsv"))

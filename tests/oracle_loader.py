@@ -83,3 +83,57 @@ def ref(real_bits: int = 32):
             _make(f"_ref/libdvr_ref{real_bits}.so")
         _cache[key] = OracleLibrary(path, f"dvrref{real_bits}_", real_bits) if os.path.exists(path) else None
     return _cache[key]
+
+
+class RefVolume:
+    """oracle/_ref/libdvr_refvol.so: the reference's own renderer::Volume (volume.cpp, volume_implicit.cpp and its
+    vendored LZ4, compiled unmodified; oracle/ref_shim_volume.cpp). Arrays are float32 [X][Y][Z]."""
+
+    def __init__(self, path):
+        self.lib = ctypes.CDLL(path)
+        self.lib.refvol_last_error.restype = ctypes.c_char_p
+
+    def _check(self, rc):
+        if rc != 0:
+            raise RuntimeError(self.lib.refvol_last_error().decode())
+
+    def create_implicit(self, equation, resolution, **params):
+        import numpy as np
+        out = np.zeros((resolution,) * 3, np.float32)
+        keys = (ctypes.c_char_p * len(params))(*[k.encode() for k in params])
+        vals = (ctypes.c_float * len(params))(*[float(v) for v in params.values()])
+        self._check(self.lib.refvol_create_implicit(int(equation), int(resolution), len(params), keys, vals,
+                                                    out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    def save(self, filename, data, world=(1.0, 1.0, 1.0), compression=0):
+        import numpy as np
+        data = np.ascontiguousarray(data, np.float32)
+        X, Y, Z = data.shape
+        self._check(self.lib.refvol_save(filename.encode(), data.ctypes.data_as(ctypes.c_void_p), X, Y, Z,
+                                         ctypes.c_double(world[0]), ctypes.c_double(world[1]),
+                                         ctypes.c_double(world[2]), int(compression)))
+
+    def load(self, filename):
+        import numpy as np
+        X, Y, Z = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        world = (ctypes.c_double * 3)()
+        self._check(self.lib.refvol_load(filename.encode(), ctypes.byref(X), ctypes.byref(Y), ctypes.byref(Z), world,
+                                         None))
+        out = np.zeros((X.value, Y.value, Z.value), np.float32)
+        self._check(self.lib.refvol_load(filename.encode(), ctypes.byref(X), ctypes.byref(Y), ctypes.byref(Z), world,
+                                         out.ctypes.data_as(ctypes.c_void_p)))
+        return out, tuple(world)
+
+
+def refvol():
+    """None when the binary is absent and cannot be built (no /root/reference, or no libtorch to link against)."""
+    if "refvol" not in _cache:
+        path = os.path.join(ORACLE_DIR, "_ref", "libdvr_refvol.so")
+        if not os.path.exists(path) and os.path.isdir("/root/reference/renderer"):
+            _make("_ref/libdvr_refvol.so")
+        try:
+            _cache["refvol"] = RefVolume(path) if os.path.exists(path) else None
+        except OSError:
+            _cache["refvol"] = None
+    return _cache["refvol"]

@@ -1,6 +1,7 @@
 #!/usr/bin/env python
-"""Kernel-level timing of the callers either side of the marcher (SURVEY 8(f) rows f1, f2) at C3 size
-(8 views @512^2, D = 6): Camera::generateRays forward / backward and Renderer::compareToImage.
+"""Kernel-level timing of the callers either side of the marcher (SURVEY 8(f) rows f1, f2, f3) at C3 size
+(8 views @512^2, D = 6; 256^3 volume): Camera::generateRays forward / backward, Renderer::compareToImage and
+renderer::Volume's producers (implicit data sets, .cvol body conversion, mipmap pooling).
 All three are streaming kernels; the figure of merit is algorithmic bytes / time against the measured
 HBM copy bandwidth (MEASURED_PEAKS.json hbm_gbs). 8 x 512^2 x 24 B = 50 MB per ray tensor fits the
 126 MB L2, so a 256 MiB buffer is written between timed launches to flush it.
@@ -62,6 +63,21 @@ def main():
          pix * (32 + 16 * D + 4 + 4 * D)),
         (f"compare_to_image reduced, D={D} (2 launches)", lambda: lib.compare_to_image(color, grads, ref, dr, gr, True, s),
          pix * (32 + 16 * D)),
+    ]
+    # renderer::Volume producers (row f3) at the configs' volume size
+    n = 256
+    vox = n ** 3
+    vol, vol2 = torch.empty(1, n, n, n, device="cuda"), torch.empty(1, n, n, n, device="cuda")
+    raw8 = torch.randint(0, 256, (vox,), dtype=torch.uint8, device="cuda")
+    raw32 = torch.rand(vox, device="cuda")
+    half = torch.empty(1, n // 2, n // 2, n // 2, device="cuda")
+    rows += [
+        (f"create_implicit_volume Sphere {n}^3", lambda: lib.create_implicit_volume(2, vol, None, s), vox * 4),
+        (f"create_implicit_volume MarschnerLobb {n}^3 (fp64 sin/cos)", lambda: lib.create_implicit_volume(0, vol, None, s), vox * 4),
+        (f"volume_from_raw u8 {n}^3 (transpose + convert)", lambda: lib.volume_from_raw(raw8, 0, vol, s), vox * 5),
+        (f"volume_from_raw f32 {n}^3 (transpose)", lambda: lib.volume_from_raw(raw32, 2, vol, s), vox * 8),
+        (f"volume_to_raw {n}^3 (transpose)", lambda: lib.volume_to_raw(vol, raw32, s), vox * 8),
+        (f"downsample_volume {n}^3 -> {n // 2}^3", lambda: lib.downsample_volume(vol, half, s), vox * 4 + vox // 2),
     ]
     print(f"| kernel ({B} views @{W}x{H}, L2 flushed between launches) | ms | algorithmic MB | GB/s | of {peak:.0f} GB/s HBM copy peak |")
     print("|---|---|---|---|---|")
