@@ -599,6 +599,8 @@ int dvr_render_forward_gradients(const DvrInputs* inputs, const DvrForwardDiffer
     const int tf = inputs->tf_mode;
     const size_t smem = check_smem(size_t(((c.ri.R * tf_row(tf) + 3) & ~3) + c.ri.R * tf_row(tf)) * sizeof(float));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    QuadScratch quads;  // one QUAD copy of the volume serves all passes
+    const int filter = maybe_build_quads(inputs->volume_filter_mode, c, quads, s);
     // ceil(D / chunk) marching passes over disjoint slot ranges
     int d0 = 0;
     while (d0 < st->D) {
@@ -606,7 +608,7 @@ int dvr_render_forward_gradients(const DvrInputs* inputs, const DvrForwardDiffer
       const int chunk = left == 1 ? 1 : (left <= 6 ? 6 : 8);
       ga.d0 = d0;
       ga.writeColor = d0 == 0;
-      after_launch(launch_forward_gradients(inputs->volume_filter_mode, tf, inputs->blend_mode, chunk,
+      after_launch(launch_forward_gradients(filter, tf, inputs->blend_mode, chunk,
                                             hasStep || hasCam, hasTf, c.ri, fo, ga, tile_grid(c), smem, s),
                    "dvr_render_forward_gradients", s);
       d0 += chunk;

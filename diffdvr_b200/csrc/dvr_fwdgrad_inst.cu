@@ -1,5 +1,5 @@
 // Instances of the forward-mode kernel for ONE (tf, blend) pair (-DDVR_TF=.. -DDVR_BL=..):
-// {Nearest, Trilinear} x chunk {1, 6, 8} x {pos, tf, pos+tf}.
+// {Nearest, Trilinear, Trilinear on the QUAD copy} x chunk {1, 6, 8} x {pos, tf, pos+tf}.
 #include "dvr_fwdgrad.cuh"
 #include "dvr_launch.h"
 
@@ -35,6 +35,7 @@ cudaError_t DVR_NAME(DVR_TF, DVR_BL)(int filter, int chunk, bool hasPos, bool ha
                                      size_t smem, cudaStream_t s) {
   if (filter == kFilterNearest) return by_chunk<kFilterNearest>(chunk, hasPos, hasTf, in, out, ga, grid, smem, s);
   if (filter == kFilterTrilinear) return by_chunk<kFilterTrilinear>(chunk, hasPos, hasTf, in, out, ga, grid, smem, s);
+  if (filter == kFilterTrilinearQuad) return by_chunk<kFilterTrilinearQuad>(chunk, hasPos, hasTf, in, out, ga, grid, smem, s);
   return cudaErrorInvalidValue;
 }
 

@@ -59,3 +59,30 @@ def test_automatic_choice_follows_the_work_estimate():
         n0 = lib.launch_count()
         gr.forward(sc, lib)
         assert lib.launch_count() - n0 == want
+
+
+@pytest.mark.parametrize("name", sorted(n for n, (_, _, fg) in CASES.items() if fg is not None))
+def test_forward_mode_quad_copy_equals_in_place_sampling(name):
+    """Forward-mode differentiation samples through the same two layouts: identical images and termination indices,
+    Jacobians equal to rounding (the dual-number x-lerp is evaluated from the same corner values) and equal to the
+    reference's fixtures within 1e-4."""
+    sc, _, fg = CASES[name]
+    st = golden_cases.fg_settings(sc, fg)
+    gold = np.load(os.path.join(GOLDEN, f"ref_{name}.npz"))
+    lib = capi.load()
+    res = {}
+    for layout in (0, 1):
+        lib.set_option("volume_layout", layout)
+        try:
+            n0 = lib.launch_count()
+            res[layout] = gr.forward_gradients(sc, lib=lib, **st)
+            launches = lib.launch_count() - n0
+        finally:
+            lib.set_option("volume_layout", -1)
+        passes = -(-st["D"] // 8) if st["D"] > 6 else 1
+        assert launches == passes + layout  # ONE copy serves every pass
+    (c0, t0, g0), (c1, t1, g1) = res[0], res[1]
+    assert np.array_equal(c0, c1) and np.array_equal(t0, t1)
+    assert scenes.rel_l2(g1, g0) <= 2e-6
+    same = t1 == gold["fg_term"]
+    assert scenes.rel_l2(g1[same], gold["fg_gradients"][same]) <= 1e-4
