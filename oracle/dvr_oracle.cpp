@@ -931,6 +931,7 @@ static void face_distance(const DvrInputs& in, const DvrTensor& termT, const Dvr
 #include "dvr_oracle_camera.h"
 #include "dvr_oracle_tfutils.h"
 #include "dvr_oracle_volume.h"
+#include "dvr_oracle_fn.h"
 namespace dvro {
 
 template <typename F>
@@ -1007,6 +1008,31 @@ using namespace dvro;
   }                                                                                                 \
   extern "C" int dvro##P##_downsample_volume(const DvrTensor* v, const DvrTensor* o, void*) {       \
     return guarded([&] { downsample_volume<R>(*v, *o); });                                          \
+  }                                                                                                 \
+  extern "C" int dvro##P##_fn_blend(int32_t mode, int32_t n, const R* x, R* out) {                  \
+    return guarded([&] { fn_blend<R>(mode, n, x, out); });                                          \
+  }                                                                                                 \
+  extern "C" int dvro##P##_fn_blend_adjoint(int32_t mode, int32_t n, const R* x, const R* e,        \
+                                            const R* g, R* z, R* accIn) {                           \
+    return guarded([&] { fn_blend_adjoint<R>(mode, n, x, e, g, z, accIn); });                       \
+  }                                                                                                 \
+  extern "C" int dvro##P##_fn_tf(int32_t mode, int32_t Rn, int32_t C, const R* tf, int32_t n,       \
+                                 const R* density, R* out) {                                        \
+    return guarded([&] { fn_tf<R>(mode, Rn, C, tf, n, density, out); });                            \
+  }                                                                                                 \
+  extern "C" int dvro##P##_fn_tf_adjoint(int32_t mode, int32_t Rn, int32_t C, const R* tf,          \
+                                         int32_t n, const R* density, const R* g, R* adjDensity,    \
+                                         R* adjTf) {                                                \
+    return guarded([&] { fn_tf_adjoint<R>(mode, Rn, C, tf, n, density, g, adjDensity, adjTf); });   \
+  }                                                                                                 \
+  extern "C" int dvro##P##_fn_interp(int32_t X, int32_t Y, int32_t Z, const R* volume, int32_t n,   \
+                                     const R* pos, R* out) {                                        \
+    return guarded([&] { fn_interp<R>(X, Y, Z, volume, n, pos, out); });                            \
+  }                                                                                                 \
+  extern "C" int dvro##P##_fn_interp_adjoint(int32_t X, int32_t Y, int32_t Z, const R* volume,      \
+                                             int32_t n, const R* pos, const R* g, R* adjPos,        \
+                                             R* adjVolume) {                                        \
+    return guarded([&] { fn_interp_adjoint<R>(X, Y, Z, volume, n, pos, g, adjPos, adjVolume); });   \
   }                                                                                                 \
   extern "C" const char* dvro##P##_last_error() { return g_error.c_str(); }                         \
   extern "C" int dvro##P##_real_size() { return int(sizeof(R)); }
