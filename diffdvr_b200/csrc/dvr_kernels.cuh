@@ -173,9 +173,12 @@ DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC
     const float dc = fmaxf(0.f, fminf(density, 1.f));
     const float sa = s_tf[0], sc = s_tf[1];
     const float adjDc = (adjC.x * sc + adjC.y * sc + adjC.z * sc) + adjC.w * sa;
-    if constexpr (HAS_TF) {
+    if constexpr (TFACC == kTfAccReg) {
       acc.g[0] += adjC.w * dc;                               // d/d scaleAbsorption
       acc.g[1] += adjC.x * dc + adjC.y * dc + adjC.z * dc;   // d/d scaleColor
+    } else if constexpr (HAS_TF) {  // never chosen by the host dispatch (two scalars fit registers); kept correct
+      const float v[2] = {adjC.w * dc, adjC.x * dc + adjC.y * dc + adjC.z * dc};
+      acc.add_row(0, v);
     }
     return (density > 0.f && density < 1.f) ? adjDc : 0.f;
   } else if constexpr (TF == kTfTexture) {  // :173-220

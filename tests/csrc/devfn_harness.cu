@@ -173,7 +173,6 @@ DEVFN_API int devfn_tf(int32_t mode, int32_t R, int32_t C, const float* tf, int3
 DEVFN_API int devfn_tf_adjoint(int32_t mode, int32_t R, int32_t C, const float* tf, int32_t n, const float* density,
                                const float* g, float* adjDensity, float* adjTf, int32_t acc) {
   const RayInputs in = tf_inputs(tf, R, C);
-  if (mode == kTfIdentity && acc != kTfAccReg) return -3;  // Identity has two scalars: register accumulators only
   if (acc == kTfAccReg) {
     if (R > kRegRows) return -2;
     TF_SWITCH(mode, (k_tf_adjoint<M, kTfAccReg><<<blocks(n), 128, size_t(R) * TfLayout<M>::kRow * 4>>>(

@@ -64,9 +64,9 @@ def test_transfer_functions(name):
         table = table.astype(np.float32)
         got = dev.tf(mode, table, densities)
         g = rng.uniform(-1, 1, got.shape).astype(np.float32)
-        # the accumulators the host dispatch can choose (dvr_capi.cu): Identity and R <= 6 -> register table,
-        # larger tables -> cached rows + atomics; the latter is exercised for every R here
-        accs = [1] if mode == capi.TF_IDENTITY else [2] + ([1] if table.shape[0] <= 6 else [])
+        # both accumulators of the host dispatch (dvr_capi.cu): register table (R <= 6) and cached rows + atomics
+        # (larger tables; exercised for every R here)
+        accs = [2] + ([1] if table.shape[0] <= 6 else [])
         for o in _oracles():
             want = o.tf(mode, table, densities)
             if mode == capi.TF_GAUSSIAN_LOG:
