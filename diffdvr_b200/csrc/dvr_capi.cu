@@ -601,7 +601,17 @@ int dvr_render_forward_gradients(const DvrInputs* inputs, const DvrForwardDiffer
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     QuadScratch quads;  // one QUAD copy of the volume serves all passes
     const int filter = maybe_build_quads(inputs->volume_filter_mode, c, quads, s);
-    // ceil(D / chunk) marching passes over disjoint slot ranges
+    if (!hasTf) {
+      // ray / stepsize tangents only: the slots are a linear map of <= 7 input tangents carried per input, ONE
+      // marching pass for any D (k_forward_gradients_inputs)
+      ga.d0 = 0;
+      ga.writeColor = 1;
+      after_launch(launch_forward_gradients(filter, tf, inputs->blend_mode, 0, true, false, c.ri, fo, ga, tile_grid(c),
+                                            smem, s),
+                   "dvr_render_forward_gradients", s);
+      return;
+    }
+    // TF tangents: ceil(D / chunk) marching passes over disjoint slot ranges
     int d0 = 0;
     while (d0 < st->D) {
       const int left = st->D - d0;

@@ -131,7 +131,7 @@ DVR_DEV Du4<N> tf_eval_dual(const float* s_tf, const int* s_dtf, int R, const DE
 
 // HAS_POS: stepsize and/or ray tangents are traced (position, t and stepsize are dual)
 template <int FILTER, int TF, int BLEND, int N, bool HAS_POS, bool HAS_TF>
-__global__ void __launch_bounds__(kThreads) k_forward_gradients(const RayInputs in, const ForwardOutputs out,
+__global__ void __launch_bounds__(kThreads, N <= 6 ? 4 : 3) k_forward_gradients(const RayInputs in, const ForwardOutputs out,
                                                                 const ForwardGradArgs ga) {
   extern __shared__ __align__(16) float smem[];
   constexpr int ROW = TfLayout<TF>::kRow;
@@ -275,6 +275,108 @@ __global__ void __launch_bounds__(kThreads) k_forward_gradients(const RayInputs 
       float* gd = g + d * ga.gD;
       gd[0] = acc.x.d[k]; gd[ga.gC] = acc.y.d[k]; gd[2 * ga.gC] = acc.z.d[k]; gd[3 * ga.gC] = acc.w.d[k];
     }
+  }
+}
+
+// Forward-mode when ONLY the ray (start, direction) and / or the stepsize are differentiated -- the camera
+// optimisation of the reference (C3; pytests/diffdvr/renderer.py:67-69). The D tangent slots are then a linear map
+// of at most seven INPUT tangents (start xyz, direction xyz, stepsize), each of which has a closed form per sample:
+//   d pos / d start_a = 1/voxel_a (axis a only),  d pos / d dir_a = t / voxel_a,  d pos / d step = i * pd,
+// so the kernel carries the accumulator's tangents per input instead of per slot: no position duals in registers
+// (42 fewer than the slot-major kernel), density tangents = cell gradient x those closed forms (10 operations per
+// sample for all seven), colour tangents = dTF/d density x density tangent (rank one), blend tangents written out per
+// input with the shared factors hoisted. ONE marching pass for any D; the slots are assembled at the end (several
+// inputs may share a slot: their tangents add, as unit seeds in the same slot would).
+template <int FILTER, int TF, int BLEND>
+__global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const RayInputs in, const ForwardOutputs out,
+                                                                          const ForwardGradArgs ga) {
+  extern __shared__ __align__(16) float smem[];
+  constexpr int NI = 7;
+  const int b = blockIdx.z;
+  float* s_tf = smem;
+  stage_tf<TF>(in, b, s_tf);
+  __syncthreads();
+  int x, y;
+  thread_pixel(x, y);
+  if (x >= in.W || y >= in.H) return;
+
+  const Ray ray = make_ray(in, x, y, b);  // box intersection on VALUES only (:201-208)
+  float ax[NI], ay[NI], az[NI], aw[NI];   // d acc / d input
+#pragma unroll
+  for (int j = 0; j < NI; ++j) ax[j] = ay[j] = az[j] = aw[j] = 0.f;
+  f4 acc = {0.f, 0.f, 0.f, 0.f};
+  Sampler<FILTER, false> smp;
+  smp.init(in, b, nullptr, 0);
+  int i = 0;
+  float fi = 0.f;
+  for (;; ++i, fi += 1.0f) {
+    const float t = sample_t(ray, fi);
+    if (t > ray.tmax) break;
+    if (acc.w > in.earlyOut) break;
+    const f3 p = sample_pos<true>(ray, t);
+    const float density = smp.fetch(in, nullptr, p.x, p.y, p.z);
+    // d density / d input
+    float dd[NI];
+    if constexpr (FILTER == kFilterNearest) {
+#pragma unroll
+      for (int j = 0; j < NI; ++j) dd[j] = 0.f;  // no positional tangent (interpolation.cuh:52-65)
+    } else {
+      const f3 g = smp.template adjoint<true>(1.0f);  // gradient of the trilinear cell at the sample
+      dd[0] = g.x * ray.invVoxel.x; dd[1] = g.y * ray.invVoxel.y; dd[2] = g.z * ray.invVoxel.z;
+      dd[3] = t * dd[0]; dd[4] = t * dd[1]; dd[5] = t * dd[2];
+      dd[6] = fi * fmaf(g.z, ray.pd.z, fmaf(g.y, ray.pd.y, g.x * ray.pd.x));
+    }
+    // colour and d colour / d density: the dual TF code with one tangent
+    Du<1> d1;
+    d1.v = density;
+    d1.d[0] = 1.0f;
+    const Du4<1> c1 = tf_eval_dual<TF, 1, false>(s_tf, nullptr, in.R, d1, 0);
+    // blend: values exactly as blend_alpha / blend_over of the plain forward kernel
+    const float wv = c1.w.v, sv = ray.step;
+    float e = 0.f, av;
+    bool active = true;
+    if constexpr (BLEND == kBlendBeer) {
+      e = blend_exp(-wv * sv);
+      av = 1.f - e;
+    } else {
+      active = !(1.f < wv * sv);
+      av = active ? wv * sv : 1.f;
+    }
+    const float om = 1.f - acc.w;
+    const float oav = om * av;
+    const float kx = c1.x.d[0] * oav, ky = c1.y.d[0] * oav, kz = c1.z.d[0] * oav, kw = c1.w.d[0] * sv;
+#pragma unroll
+    for (int j = 0; j < NI; ++j) {
+      float ws = kw * dd[j];            // (w s)' = w' s + w s', s' = 1 for the stepsize input only
+      if (j == 6) ws += wv;
+      float ad;
+      if constexpr (BLEND == kBlendBeer) ad = e * ws;
+      else ad = active ? ws : 0.f;
+      const float oad = fmaf(-aw[j], av, om * ad);  // d((1 - acc.w) alpha)
+      ax[j] += fmaf(kx, dd[j], c1.x.v * oad);
+      ay[j] += fmaf(ky, dd[j], c1.y.v * oad);
+      az[j] += fmaf(kz, dd[j], c1.z.v * oad);
+      aw[j] += oad;
+    }
+    acc.x = fmaf(om * c1.x.v, av, acc.x);
+    acc.y = fmaf(om * c1.y.v, av, acc.y);
+    acc.z = fmaf(om * c1.z.v, av, acc.z);
+    acc.w = fmaf(om, av, acc.w);
+  }
+  float* c = out.color + b * out.cB + y * out.cY + x * out.cX;
+  c[0] = acc.x; c[out.cC] = acc.y; c[2 * out.cC] = acc.z; c[3 * out.cC] = acc.w;
+  out.term[b * out.tB + y * out.tY + x * out.tX] = i;
+  // slots <- inputs
+  float* g = ga.grad + b * ga.gB + y * ga.gY + x * ga.gX;
+  for (int d = 0; d < ga.D; ++d) {
+    float gx = 0.f, gy = 0.f, gz = 0.f, gw = 0.f;
+#pragma unroll
+    for (int j = 0; j < NI; ++j) {
+      const int slot = j < 3 ? ga.dRayStart[j] : (j < 6 ? ga.dRayDir[j - 3] : ga.dStep);
+      if (slot == d) { gx += ax[j]; gy += ay[j]; gz += az[j]; gw += aw[j]; }
+    }
+    float* gd = g + d * ga.gD;
+    gd[0] = gx; gd[ga.gC] = gy; gd[2 * ga.gC] = gz; gd[3 * ga.gC] = gw;
   }
 }
 

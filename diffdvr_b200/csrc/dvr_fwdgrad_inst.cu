@@ -23,6 +23,9 @@ template <int F>
 static cudaError_t by_chunk(int n, bool p, bool t, const RayInputs& in, const ForwardOutputs& out,
                             const ForwardGradArgs& ga, dim3 g, size_t sm, cudaStream_t s) {
   switch (n) {
+    case 0:  // input-major single pass: ray / stepsize tangents only (k_forward_gradients_inputs)
+      if (!p || t) return cudaErrorInvalidValue;
+      return launch_kernel(k_forward_gradients_inputs<F, DVR_TF, DVR_BL>, g, kThreads, sm, s, in, out, ga);
     case 1: return by_flags<F, 1>(p, t, in, out, ga, g, sm, s);
     case 6: return by_flags<F, 6>(p, t, in, out, ga, g, sm, s);
     case 8: return by_flags<F, 8>(p, t, in, out, ga, g, sm, s);

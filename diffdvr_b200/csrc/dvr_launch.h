@@ -17,7 +17,7 @@ cudaError_t launch_adjoint(int filter, int tf, int blend, bool hasVol, int tfacc
                            const RayInputs& in, const AdjointArgs& aa, dim3 grid, size_t smem,
                            cudaStream_t stream);
 
-// chunk: number of tangent slots per pass (1, 6 or 8)
+// chunk: number of tangent slots per pass (1, 6 or 8); 0 = the input-major single pass (ray / stepsize tangents only)
 cudaError_t launch_forward_gradients(int filter, int tf, int blend, int chunk, bool hasPos, bool hasTf,
                                      const RayInputs& in, const ForwardOutputs& out,
                                      const ForwardGradArgs& ga, dim3 grid, size_t smem,
