@@ -129,7 +129,8 @@ DVR_DEV Du4<N> tf_eval_dual(const float* s_tf, const int* s_dtf, int R, const DE
   }
 }
 
-// HAS_POS: stepsize and/or ray tangents are traced (position, t and stepsize are dual)
+// Slot-major kernel for TF tangents (HAS_TF; instantiated for HAS_TF only). HAS_POS: stepsize and / or ray tangents
+// are traced as well (position, t and stepsize are dual).
 template <int FILTER, int TF, int BLEND, int N, bool HAS_POS, bool HAS_TF>
 __global__ void __launch_bounds__(kThreads, N <= 6 ? 4 : 3) k_forward_gradients(const RayInputs in, const ForwardOutputs out,
                                                                 const ForwardGradArgs ga) {
@@ -181,32 +182,6 @@ __global__ void __launch_bounds__(kThreads, N <= 6 ? 4 : 3) k_forward_gradients(
       Du<N> dd;
       if constexpr (FILTER == kFilterNearest) {
         dd = du_const<N>(density);  // no positional tangent (interpolation.cuh:52-65)
-      } else if constexpr (!HAS_TF) {
-        // Only the sample position carries tangents here, and density = trilinear(pos), colour = TF(density) are
-        // scalar functions of it: their N tangents are rank one. Instead of pushing N tangents through seven
-        // lerps and the whole TF (Gaussian: R exponentials' worth of dual arithmetic), take the spatial gradient
-        // of the cell (3 values, the adjoint sampler's formula) and dTF/d density (4 values, the same dual TF
-        // code with ONE tangent), then one dot product and four products per tangent slot.
-        const f3 gpos = smp.template adjoint<true>(1.0f);
-        dd.v = density;
-#pragma unroll
-        for (int k = 0; k < N; ++k) {
-          const float tk = step.d[k] * fi;  // dt/d slot: t = tmin + i * step
-          const float px = psx.d[k] + fmaf(tk, pdx.v, t * pdx.d[k]);
-          const float py = psy.d[k] + fmaf(tk, pdy.v, t * pdy.d[k]);
-          const float pz = psz.d[k] + fmaf(tk, pdz.v, t * pdz.d[k]);
-          dd.d[k] = fmaf(gpos.z, pz, fmaf(gpos.y, py, gpos.x * px));
-        }
-        Du<1> d1;
-        d1.v = density;
-        d1.d[0] = 1.0f;
-        const Du4<1> c1 = tf_eval_dual<TF, 1, false>(s_tf, s_dtf, in.R, d1, 0);
-        cur.x.v = c1.x.v; cur.y.v = c1.y.v; cur.z.v = c1.z.v; cur.w.v = c1.w.v;
-#pragma unroll
-        for (int k = 0; k < N; ++k) {
-          cur.x.d[k] = c1.x.d[0] * dd.d[k]; cur.y.d[k] = c1.y.d[0] * dd.d[k];
-          cur.z.d[k] = c1.z.d[0] * dd.d[k]; cur.w.d[k] = c1.w.d[0] * dd.d[k];
-        }
       } else {
         // t = tmin + i*step: dt/dstep = i; positions keep the value computed above
         Du<N> td = step * fi;
@@ -217,7 +192,7 @@ __global__ void __launch_bounds__(kThreads, N <= 6 ? 4 : 3) k_forward_gradients(
         dd = du_lerp(du_lerp(du_lerp(d[0], d[4], fxd), du_lerp(d[2], d[6], fxd), fyd),
                      du_lerp(du_lerp(d[1], d[5], fxd), du_lerp(d[3], d[7], fxd), fyd), fzd);
       }
-      if constexpr (HAS_TF || FILTER == kFilterNearest) cur = tf_eval_dual<TF, N, HAS_TF>(s_tf, s_dtf, in.R, dd, d0);
+      cur = tf_eval_dual<TF, N, HAS_TF>(s_tf, s_dtf, in.R, dd, d0);
     } else {
       cur = tf_eval_dual<TF, N, HAS_TF>(s_tf, s_dtf, in.R, density, d0);
     }

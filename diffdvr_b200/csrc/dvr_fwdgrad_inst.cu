@@ -1,5 +1,5 @@
 // Instances of the forward-mode kernel for ONE (tf, blend) pair (-DDVR_TF=.. -DDVR_BL=..):
-// {Nearest, Trilinear, Trilinear on the QUAD copy} x chunk {1, 6, 8} x {pos, tf, pos+tf}.
+// {Nearest, Trilinear, Trilinear on the QUAD copy} x ({input-major} + chunk {1, 6, 8} x {tf, pos+tf}).
 #include "dvr_fwdgrad.cuh"
 #include "dvr_launch.h"
 
@@ -15,7 +15,7 @@ template <int F, int N>
 static cudaError_t by_flags(bool p, bool t, const RayInputs& in, const ForwardOutputs& out,
                             const ForwardGradArgs& ga, dim3 g, size_t sm, cudaStream_t s) {
   if (p && t) return launch_kernel(k_forward_gradients<F, DVR_TF, DVR_BL, N, true, true>, g, kThreads, sm, s, in, out, ga);
-  if (p) return launch_kernel(k_forward_gradients<F, DVR_TF, DVR_BL, N, true, false>, g, kThreads, sm, s, in, out, ga);
+  // ray / stepsize tangents without TF tangents go through k_forward_gradients_inputs (chunk 0)
   if (t) return launch_kernel(k_forward_gradients<F, DVR_TF, DVR_BL, N, false, true>, g, kThreads, sm, s, in, out, ga);
   return cudaErrorInvalidValue;
 }
