@@ -299,7 +299,7 @@ DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC
 }
 
 template <int FILTER, int TF, int BLEND, bool HAS_VOL, int TFACC, bool HAS_RAY>
-__global__ void __launch_bounds__(kThreads) k_adjoint(const RayInputs in, const AdjointArgs aa) {
+__global__ void __launch_bounds__(kThreads, HAS_RAY ? 6 : 1) k_adjoint(const RayInputs in, const AdjointArgs aa) {
   extern __shared__ __align__(16) float smem[];
   constexpr int ROW = TfLayout<TF>::kRow;
   constexpr int CH = TfChannels<TF>::v;
