@@ -299,6 +299,8 @@ DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC
 }
 
 template <int FILTER, int TF, int BLEND, bool HAS_VOL, int TFACC, bool HAS_RAY>
+// HAS_RAY instances: <= 80 registers for 6 CTAs/SM (C3 adjoint(camera) 26.2 -> 24.8 ms). Forcing more CTAs on the
+// others (forward <= 40 registers, adjoint(volume) <= 48) was measured and is slower: they are issue bound.
 __global__ void __launch_bounds__(kThreads, HAS_RAY ? 6 : 1) k_adjoint(const RayInputs in, const AdjointArgs aa) {
   extern __shared__ __align__(16) float smem[];
   constexpr int ROW = TfLayout<TF>::kRow;
