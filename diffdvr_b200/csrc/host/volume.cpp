@@ -79,7 +79,10 @@ void decompressBody(std::istream& s, uint8_t* dst, size_t bytes, const std::stri
   while (pos < bytes) {
     int32_t n = 0;
     s.read(reinterpret_cast<char*>(&n), 4);
-    if (!s || n <= 0) throw std::runtime_error("truncated or malformed LZ4 chunk in " + what);
+    // a chunk holds at most 64 KiB of input, so at most LZ4's worst-case bound of that (the reference reads into a
+    // buffer of exactly this size without checking, lz4cpp.cpp:92-104)
+    constexpr int32_t kMaxBlock = lz4::kMaxChunk + lz4::kMaxChunk / 255 + 16;
+    if (!s || n <= 0 || n > kMaxBlock) throw std::runtime_error("truncated or malformed LZ4 chunk in " + what);
     block.resize(size_t(n));
     s.read(reinterpret_cast<char*>(block.data()), n);
     if (!s) throw std::runtime_error("truncated LZ4 chunk in " + what);

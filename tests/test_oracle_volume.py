@@ -140,6 +140,8 @@ def test_product_decoder_rejects_malformed_streams():
         pyr.cvol_decompress_body(bytes(bad), 64)
     with pytest.raises(Exception):
         pyr.cvol_decompress_body((0).to_bytes(4, "little"), 8)              # empty chunk
+    with pytest.raises(Exception):
+        pyr.cvol_decompress_body((1 << 30).to_bytes(4, "little") + bytes(100), 8)  # absurd chunk size: no 1 GiB alloc
 
 
 @pytest.mark.parametrize("level", [1, 3, 9])
