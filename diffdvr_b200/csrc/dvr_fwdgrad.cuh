@@ -301,13 +301,31 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
       dd[3] = t * dd[0]; dd[4] = t * dd[1]; dd[5] = t * dd[2];
       dd[6] = fi * fmaf(g.z, ray.pd.z, fmaf(g.y, ray.pd.y, g.x * ray.pd.x));
     }
-    // colour and d colour / d density: the dual TF code with one tangent
-    Du<1> d1;
-    d1.v = density;
-    d1.d[0] = 1.0f;
-    const Du4<1> c1 = tf_eval_dual<TF, 1, false>(s_tf, nullptr, in.R, d1, 0);
+    // colour cv and its slope cs = d colour / d density
+    f4 cv, cs;
+    if constexpr (TF == kTfGaussian) {
+      // the plain kernel's evaluation (tf_eval: staged reciprocals, one expf per row) plus, per row,
+      // d/dd exp(-(d - mu)^2 / 2 sigma^2) = n (mu - d) / sigma^2 as in tf_adjoint
+      cv = {0.f, 0.f, 0.f, 0.f};
+      cs = {0.f, 0.f, 0.f, 0.f};
+      for (int r = 0; r < in.R; ++r) {
+        const float* row = s_tf + 8 * r;
+        const f4 ci = lds4(row);
+        const float n = expf(gauss_arg(density, row));
+        const float k = n * div_rcp(row[4] - density, row[5] * row[5], row[7]);
+        cv.x = fmaf(ci.x, n, cv.x); cv.y = fmaf(ci.y, n, cv.y); cv.z = fmaf(ci.z, n, cv.z); cv.w = fmaf(ci.w, n, cv.w);
+        cs.x = fmaf(ci.x, k, cs.x); cs.y = fmaf(ci.y, k, cs.y); cs.z = fmaf(ci.z, k, cs.z); cs.w = fmaf(ci.w, k, cs.w);
+      }
+    } else {  // the dual TF code with one tangent
+      Du<1> d1;
+      d1.v = density;
+      d1.d[0] = 1.0f;
+      const Du4<1> c1 = tf_eval_dual<TF, 1, false>(s_tf, nullptr, in.R, d1, 0);
+      cv = {c1.x.v, c1.y.v, c1.z.v, c1.w.v};
+      cs = {c1.x.d[0], c1.y.d[0], c1.z.d[0], c1.w.d[0]};
+    }
     // blend: values exactly as blend_alpha / blend_over of the plain forward kernel
-    const float wv = c1.w.v, sv = ray.step;
+    const float wv = cv.w, sv = ray.step;
     float e = 0.f, av;
     bool active = true;
     if constexpr (BLEND == kBlendBeer) {
@@ -319,7 +337,7 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
     }
     const float om = 1.f - acc.w;
     const float oav = om * av;
-    const float kx = c1.x.d[0] * oav, ky = c1.y.d[0] * oav, kz = c1.z.d[0] * oav, kw = c1.w.d[0] * sv;
+    const float kx = cs.x * oav, ky = cs.y * oav, kz = cs.z * oav, kw = cs.w * sv;
 #pragma unroll
     for (int j = 0; j < NI; ++j) {
       float ws = kw * dd[j];            // (w s)' = w' s + w s', s' = 1 for the stepsize input only
@@ -328,14 +346,14 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
       if constexpr (BLEND == kBlendBeer) ad = e * ws;
       else ad = active ? ws : 0.f;
       const float oad = fmaf(-aw[j], av, om * ad);  // d((1 - acc.w) alpha)
-      ax[j] += fmaf(kx, dd[j], c1.x.v * oad);
-      ay[j] += fmaf(ky, dd[j], c1.y.v * oad);
-      az[j] += fmaf(kz, dd[j], c1.z.v * oad);
+      ax[j] += fmaf(kx, dd[j], cv.x * oad);
+      ay[j] += fmaf(ky, dd[j], cv.y * oad);
+      az[j] += fmaf(kz, dd[j], cv.z * oad);
       aw[j] += oad;
     }
-    acc.x = fmaf(om * c1.x.v, av, acc.x);
-    acc.y = fmaf(om * c1.y.v, av, acc.y);
-    acc.z = fmaf(om * c1.z.v, av, acc.z);
+    acc.x = fmaf(om * cv.x, av, acc.x);
+    acc.y = fmaf(om * cv.y, av, acc.y);
+    acc.z = fmaf(om * cv.z, av, acc.z);
     acc.w = fmaf(om, av, acc.w);
   }
   float* c = out.color + b * out.cB + y * out.cY + x * out.cX;
