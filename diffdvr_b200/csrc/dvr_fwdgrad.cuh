@@ -57,6 +57,8 @@ template <int N> DVR_DEV Du<N> operator/(const Du<N>& a, const Du<N>& b) {
 template <int N> DVR_DEV Du<N> operator/(const Du<N>& a, float b) { return a * (1.0f / b); }
 template <int N> DVR_DEV Du<N> du_exp(const Du<N>& a) { Du<N> r; r.v = expf(a.v); DVR_DU_LOOP r.d[i] = a.d[i] * r.v; return r; }
 DVR_DEV float du_exp(float a) { return expf(a); }
+// exp of the Gaussian TF kernel: the same gauss_exp as the other kernels
+template <int N> DVR_DEV Du<N> du_gauss_exp(const Du<N>& a) { Du<N> r; r.v = gauss_exp(a.v); DVR_DU_LOOP r.d[i] = a.d[i] * r.v; return r; }
 // exp of the Beer-Lambert blend: the same blend_exp as the plain forward kernel, so both write the same colour
 template <int N> DVR_DEV Du<N> du_blend_exp(const Du<N>& a) { Du<N> r; r.v = blend_exp(a.v); DVR_DU_LOOP r.d[i] = a.d[i] * r.v; return r; }
 DVR_DEV float du_blend_exp(float a) { return blend_exp(a); }
@@ -119,7 +121,7 @@ DVR_DEV Du4<N> tf_eval_dual(const float* s_tf, const int* s_dtf, int R, const DE
     for (int i = 0; i < R; ++i) {
       const auto mu = seed(i, 4), sigma = seed(i, 5);
       const Du<N> diff = dd - mu;
-      const Du<N> ni = du_exp(-(diff * diff) / (2.0f * sigma * sigma));
+      const Du<N> ni = du_gauss_exp(-(diff * diff) / (2.0f * sigma * sigma));
       c.x = c.x + seed(i, 0) * ni;
       c.y = c.y + seed(i, 1) * ni;
       c.z = c.z + seed(i, 2) * ni;
@@ -311,7 +313,7 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
       for (int r = 0; r < in.R; ++r) {
         const float* row = s_tf + 8 * r;
         const f4 ci = lds4(row);
-        const float n = expf(gauss_arg(density, row));
+        const float n = gauss_exp(gauss_arg(density, row));
         const float k = n * div_rcp(row[4] - density, row[5] * row[5], row[7]);
         cv.x = fmaf(ci.x, n, cv.x); cv.y = fmaf(ci.y, n, cv.y); cv.z = fmaf(ci.z, n, cv.z); cv.w = fmaf(ci.w, n, cv.w);
         cs.x = fmaf(ci.x, k, cs.x); cs.y = fmaf(ci.y, k, cs.y); cs.z = fmaf(ci.z, k, cs.z); cs.w = fmaf(ci.w, k, cs.w);

@@ -150,13 +150,13 @@ DVR_DEV f4 tf_eval_cached(const float* s_tf, int R, float density, float (&ni)[k
       ni[i] = 0.f;
       if (i < R) {
         const f4 ci = lds4(s_tf + 8 * i);
-        ni[i] = expf(gauss_arg(density, s_tf + 8 * i));
+        ni[i] = gauss_exp(gauss_arg(density, s_tf + 8 * i));
         c.x = fmaf(ci.x, ni[i], c.x); c.y = fmaf(ci.y, ni[i], c.y); c.z = fmaf(ci.z, ni[i], c.z); c.w = fmaf(ci.w, ni[i], c.w);
       }
     }
     for (int i = kRegRows; i < R; ++i) {
       const f4 ci = lds4(s_tf + 8 * i);
-      const float n = expf(gauss_arg(density, s_tf + 8 * i));
+      const float n = gauss_exp(gauss_arg(density, s_tf + 8 * i));
       c.x = fmaf(ci.x, n, c.x); c.y = fmaf(ci.y, n, c.y); c.z = fmaf(ci.z, n, c.z); c.w = fmaf(ci.w, n, c.w);
     }
     return c;
@@ -245,7 +245,7 @@ DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC
         }
       for (int i = kRegRows; i < R; ++i) {
         float g[6];
-        body(i, g, expf(gauss_arg(density, s_tf + 8 * i)));
+        body(i, g, gauss_exp(gauss_arg(density, s_tf + 8 * i)));
         if constexpr (HAS_TF) acc.add_row(i, g);
       }
     }
