@@ -111,8 +111,9 @@ class DeviceFns:
         import torch
         self.torch = torch
         path = os.path.join(ROOT, "tests", "_build", "libdvr_devfn.so")
-        if not os.path.exists(path):
-            raise RuntimeError(f"{path} not built (python -c 'import __graft_entry__ as g; g.build()')")
+        if not os.path.exists(path):  # normally built by __graft_entry__.build(); nvcc is on the GPU box too
+            import subprocess
+            subprocess.run(["make", "-C", os.path.join(ROOT, "tests", "csrc")], check=True, capture_output=True)
         self.lib = ctypes.CDLL(path)
 
     def _call(self, name, *args):
