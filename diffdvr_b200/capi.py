@@ -89,15 +89,57 @@ class DvrAdjointOutputs(ctypes.Structure):
     ]
 
 
-def tensor_view(t) -> DvrTensor:
-    """DvrTensor over a torch tensor or numpy array (no copy; keep ``t`` alive)."""
+class DvrCallOptions(ctypes.Structure):
+    """include/dvr_b200.h DvrCallOptions (ABI version 2)."""
+    _fields_ = [
+        ("struct_size", ctypes.c_uint32),
+        ("volume_layout", ctypes.c_int32),
+        ("compat_stepsize_overwrite", ctypes.c_int32),
+        ("sync", ctypes.c_int32),
+        ("max_scratch_bytes", ctypes.c_int64),
+        ("workspace", ctypes.c_void_p),
+    ]
+
+
+def make_call_options(volume_layout: int = -1, compat_stepsize_overwrite: bool = False, sync: bool = False,
+                      max_scratch_bytes: int = 0, workspace=None) -> DvrCallOptions:
+    o = DvrCallOptions()
+    o.struct_size = ctypes.sizeof(DvrCallOptions)
+    o.volume_layout = int(volume_layout)
+    o.compat_stepsize_overwrite = int(bool(compat_stepsize_overwrite))
+    o.sync = int(bool(sync))
+    o.max_scratch_bytes = int(max_scratch_bytes)
+    o.workspace = workspace.handle if workspace is not None else None
+    o._keep = workspace
+    return o
+
+
+def _check_tensor(t, what: str):
+    """The reference's CHECK_CUDA / CHECK_DTYPE (renderer/pytorch_utils.h:5-19) for the ctypes path: the C-ABI sees
+    raw pointers, so dtype and device are validated here. numpy arrays (the CPU oracles of the tests) only get the
+    dtype check."""
+    name = str(t.dtype).replace("torch.", "")
+    if name not in ("float32", "float64", "int32"):
+        raise TypeError(f"{what}: dtype {name} is not supported by the C-ABI (float32 / int32; float64 for the fp64 test oracle)")
+
+
+def tensor_view(t, device=None, dtype=None, what: str = "tensor") -> DvrTensor:
+    """DvrTensor over a torch tensor or numpy array (no copy; keep ``t`` alive). ``device`` (a torch device) and
+    ``dtype`` (a name such as "float32") are enforced when given."""
     v = DvrTensor()
     if t is None:
         return v
+    _check_tensor(t, what)
+    if dtype is not None and str(t.dtype).replace("torch.", "") != dtype:
+        raise TypeError(f"{what} must be {dtype}, but is {str(t.dtype).replace('torch.', '')}")
     if hasattr(t, "data_ptr"):  # torch
+        if device is not None and t.device != device:
+            raise ValueError(f"{what} must live on {device}, but is on {t.device}")
         v.ptr = t.data_ptr()
         shape, strides = tuple(t.shape), tuple(t.stride())
     else:  # numpy
+        if device is not None:
+            raise ValueError(f"{what} must be a CUDA tensor on {device}, but is a host array")
         v.ptr = t.ctypes.data
         shape = tuple(t.shape)
         strides = tuple(s // t.itemsize for s in t.strides)
@@ -259,6 +301,10 @@ class Library:
         f.restype = ctypes.c_int
         f.argtypes = argtypes
 
+    @staticmethod
+    def _stream(stream):
+        return 0 if stream is None else stream
+
     def last_error(self) -> str:
         return getattr(self.lib, self.prefix + "last_error")().decode()
 
@@ -267,79 +313,79 @@ class Library:
             raise DvrError(rc, self.last_error())
 
     # -- the four entry points -------------------------------------------------------------
-    def render_forward(self, inputs: Inputs, color, termination_index, stream: int = 0):
+    def render_forward(self, inputs: Inputs, color, termination_index, stream=None):
         ci, co = inputs.to_c(), make_outputs(color, termination_index)
-        self._check(getattr(self.lib, self.prefix + "render_forward")(ci, co, stream))
+        self._check(getattr(self.lib, self.prefix + "render_forward")(ci, co, self._stream(stream)))
 
     def render_forward_gradients(self, inputs: Inputs, settings: DvrForwardDifferencesSettings,
-                                 color, termination_index, gradients_out, stream: int = 0):
+                                 color, termination_index, gradients_out, stream=None):
         ci, co, g = inputs.to_c(), make_outputs(color, termination_index), tensor_view(gradients_out)
         self._check(getattr(self.lib, self.prefix + "render_forward_gradients")(ci, settings, co, g,
-                                                                               stream))
+                                                                               self._stream(stream)))
 
     def forward_variables_to_gradients(self, forward_variables, grad_output_color,
                                        settings: DvrForwardDifferencesSettings,
-                                       adj: DvrAdjointOutputs, stream: int = 0):
+                                       adj: DvrAdjointOutputs, stream=None):
         fv, gc = tensor_view(forward_variables), tensor_view(grad_output_color)
         self._check(getattr(self.lib, self.prefix + "forward_variables_to_gradients")(
-            fv, gc, settings, adj, stream))
+            fv, gc, settings, adj, self._stream(stream)))
 
     def render_adjoint(self, inputs: Inputs, color, termination_index, adj_color,
-                       adj: DvrAdjointOutputs, stream: int = 0):
+                       adj: DvrAdjointOutputs, stream=None):
         ci, co, ac = inputs.to_c(), make_outputs(color, termination_index), tensor_view(adj_color)
-        self._check(getattr(self.lib, self.prefix + "render_adjoint")(ci, co, ac, adj, stream))
+        self._check(getattr(self.lib, self.prefix + "render_adjoint")(ci, co, ac, adj, self._stream(stream)))
 
     # -- Camera::generateRays / Renderer::compareToImage --------------------------------------
-    def generate_rays(self, viewport, fov_y_radians, ray_start, ray_dir, stream: int = 0):
+    def generate_rays(self, viewport, fov_y_radians, ray_start, ray_dir, stream=None):
         """viewport B*3*3 -> ray_start, ray_dir B*H*W*3 (written)."""
         H, W = int(ray_start.shape[1]), int(ray_start.shape[2])
         self._check(getattr(self.lib, self.prefix + "generate_rays")(
             tensor_view(viewport), float(fov_y_radians), W, H, tensor_view(ray_start), tensor_view(ray_dir),
-            stream))
+            self._stream(stream)))
 
     def generate_rays_adjoint(self, viewport, fov_y_radians, adj_ray_start, adj_ray_dir, adj_viewport,
-                              stream: int = 0):
+                              stream=None):
         """adj_viewport (B*3*3) is overwritten with the per-view sums."""
         self._check(getattr(self.lib, self.prefix + "generate_rays_adjoint")(
             tensor_view(viewport), float(fov_y_radians), tensor_view(adj_ray_start), tensor_view(adj_ray_dir),
-            tensor_view(adj_viewport), stream))
+            tensor_view(adj_viewport), self._stream(stream)))
 
     def compare_to_image(self, color_input, gradients_input, color_reference, difference_out, gradients_out,
-                         reduce: bool = False, stream: int = 0):
+                         reduce: bool = False, stream=None):
         self._check(getattr(self.lib, self.prefix + "compare_to_image")(
             tensor_view(color_input), tensor_view(gradients_input), tensor_view(color_reference),
-            tensor_view(difference_out), tensor_view(gradients_out), int(bool(reduce)), stream))
+            tensor_view(difference_out), tensor_view(gradients_out), int(bool(reduce)), self._stream(stream)))
 
     # -- TFUtils::preshadeVolume --------------------------------------------------------------------
-    def preshade_volume(self, density_volume, tf, tf_mode, color_out, stream: int = 0):
+    def preshade_volume(self, density_volume, tf, tf_mode, color_out, stream=None):
         """density_volume 1*X*Y*Z, tf 1*R*C -> color_out 4*X*Y*Z (written)."""
         self._check(getattr(self.lib, self.prefix + "preshade_volume")(
-            tensor_view(density_volume), tensor_view(tf), int(tf_mode), tensor_view(color_out), stream))
+            tensor_view(density_volume), tensor_view(tf), int(tf_mode), tensor_view(color_out), self._stream(stream)))
 
-    def preshade_volume_adjoint(self, density_volume, tf, tf_mode, adj_color, adj_volume_out, stream: int = 0):
+    def preshade_volume_adjoint(self, density_volume, tf, tf_mode, adj_color, adj_volume_out, stream=None):
         """adj_volume_out (1*X*Y*Z) is overwritten."""
         self._check(getattr(self.lib, self.prefix + "preshade_volume_adjoint")(
             tensor_view(density_volume), tensor_view(tf), int(tf_mode), tensor_view(adj_color),
-            tensor_view(adj_volume_out), stream))
+            tensor_view(adj_volume_out), self._stream(stream)))
 
     # -- renderer::Volume producers -----------------------------------------------------------------
-    def create_implicit_volume(self, equation, volume_out, params=None, stream: int = 0):
+    def create_implicit_volume(self, equation, volume_out, params=None, stream=None):
         """volume_out 1*n*n*n (written); params = (fM, alpha, scale, a) or None for the reference's defaults."""
         p = (ctypes.c_float * 4)(*[float(v) for v in params]) if params is not None else None
         self._check(getattr(self.lib, self.prefix + "create_implicit_volume")(
-            int(equation), p, tensor_view(volume_out), stream))
+            int(equation), p, tensor_view(volume_out), self._stream(stream)))
 
-    def volume_from_raw(self, raw, dtype, volume_out, stream: int = 0):
+    def volume_from_raw(self, raw, dtype, volume_out, stream=None):
         """raw: flat u8 / u16 / f32 array or tensor of X*Y*Z elements, X fastest (.cvol body); dtype 0 / 1 / 2."""
         self._check(getattr(self.lib, self.prefix + "volume_from_raw")(
-            _data_ptr(raw), int(dtype), tensor_view(volume_out), stream))
+            _data_ptr(raw), int(dtype), tensor_view(volume_out), self._stream(stream)))
 
-    def volume_to_raw(self, volume, raw_out, stream: int = 0):
-        self._check(getattr(self.lib, self.prefix + "volume_to_raw")(tensor_view(volume), _data_ptr(raw_out), stream))
+    def volume_to_raw(self, volume, raw_out, stream=None):
+        self._check(getattr(self.lib, self.prefix + "volume_to_raw")(tensor_view(volume), _data_ptr(raw_out), self._stream(stream)))
 
-    def downsample_volume(self, volume, volume_out, stream: int = 0):
+    def downsample_volume(self, volume, volume_out, stream=None):
         self._check(getattr(self.lib, self.prefix + "downsample_volume")(
-            tensor_view(volume), tensor_view(volume_out), stream))
+            tensor_view(volume), tensor_view(volume_out), self._stream(stream)))
 
 
 def _data_ptr(a):
@@ -371,6 +417,94 @@ class ProductLibrary(Library):
         L.dvr_check_inputs.restype = ctypes.c_int
         L.dvr_check_inputs.argtypes = [ctypes.POINTER(DvrInputs)] + [ctypes.POINTER(ctypes.c_int32)] * 4
 
+        P = ctypes.POINTER
+        L.dvr_render_forward_ex.restype = ctypes.c_int
+        L.dvr_render_forward_ex.argtypes = [P(DvrInputs), P(DvrOutputs), P(DvrCallOptions), ctypes.c_void_p]
+        L.dvr_render_forward_gradients_ex.restype = ctypes.c_int
+        L.dvr_render_forward_gradients_ex.argtypes = [P(DvrInputs), P(DvrForwardDifferencesSettings), P(DvrOutputs),
+                                                      P(DvrTensor), P(DvrCallOptions), ctypes.c_void_p]
+        L.dvr_render_adjoint_ex.restype = ctypes.c_int
+        L.dvr_render_adjoint_ex.argtypes = [P(DvrInputs), P(DvrOutputs), P(DvrTensor), P(DvrAdjointOutputs),
+                                            P(DvrCallOptions), ctypes.c_void_p]
+        L.dvr_call_options_init.restype = None
+        L.dvr_call_options_init.argtypes = [P(DvrCallOptions)]
+        L.dvr_workspace_create.restype = ctypes.c_void_p
+        L.dvr_workspace_create.argtypes = []
+        L.dvr_workspace_destroy.restype = None
+        L.dvr_workspace_destroy.argtypes = [ctypes.c_void_p]
+        L.dvr_workspace_bytes.restype = ctypes.c_int64
+        L.dvr_workspace_bytes.argtypes = [ctypes.c_void_p]
+        L.dvr_workspace_invalidate.restype = ctypes.c_int
+        L.dvr_workspace_invalidate.argtypes = [ctypes.c_void_p]
+        for f in (L.dvr_workspace_set_volume, L.dvr_workspace_begin_volume_gradient,
+                  L.dvr_workspace_end_volume_gradient):
+            f.restype = ctypes.c_int
+            f.argtypes = [ctypes.c_void_p, P(DvrTensor), ctypes.c_void_p]
+        L.dvr_trim_scratch.restype = ctypes.c_int
+        L.dvr_trim_scratch.argtypes = []
+        L.dvr_get_stat.restype = ctypes.c_int
+        L.dvr_get_stat.argtypes = [ctypes.c_char_p, P(ctypes.c_int64)]
+        L.dvr_has_variant_pass.restype = ctypes.c_int
+        L.dvr_has_variant_pass.argtypes = [ctypes.c_int32] * 5
+
+    # -- validation the C-ABI cannot do (it sees raw pointers): device, dtype; default stream ------------------
+    @staticmethod
+    def _stream(stream):
+        if stream is not None:
+            return stream
+        import torch
+        return torch.cuda.current_stream().cuda_stream
+
+    @staticmethod
+    def _validate(inputs: Inputs, extra):
+        """Every tensor must be a CUDA tensor on the volume's device with the dtype the kernels read (the
+        reference's CHECK_CUDA / CHECK_DTYPE, renderer/renderer.cpp:49-263)."""
+        vol = inputs.volume
+        if not hasattr(vol, "is_cuda") or not vol.is_cuda:
+            raise ValueError("volume must be a CUDA tensor: the product has no CPU path")
+        dev = vol.device
+        named = [("volume", vol, "float32"), ("tf", inputs.tf, "float32"),
+                 ("boxMin", inputs.box_min, "float32"), ("boxSize", inputs.box_size, "float32"),
+                 ("cameraRayStart", inputs.camera_ray_start, "float32"), ("cameraRayDir", inputs.camera_ray_dir, "float32"),
+                 ("cameraMatrix", inputs.camera_matrix, "float32"), ("stepSize", inputs.step_size, "float32")] + list(extra)
+        for name, t, dtype in named:
+            if t is None or not _is_tensor(t):
+                continue
+            tensor_view(t, device=dev, dtype=dtype, what=name)
+
+    def render_forward(self, inputs: Inputs, color, termination_index, stream=None, options: DvrCallOptions = None):
+        self._validate(inputs, [("color", color, "float32"), ("terminationIndex", termination_index, "int32")])
+        ci, co = inputs.to_c(), make_outputs(color, termination_index)
+        self._check(self.lib.dvr_render_forward_ex(ci, co, options, self._stream(stream)))
+
+    def render_forward_gradients(self, inputs: Inputs, settings: DvrForwardDifferencesSettings, color,
+                                 termination_index, gradients_out, stream=None, options: DvrCallOptions = None):
+        self._validate(inputs, [("color", color, "float32"), ("terminationIndex", termination_index, "int32"),
+                                ("gradientsOut", gradients_out, "float32")])
+        ci, co, g = inputs.to_c(), make_outputs(color, termination_index), tensor_view(gradients_out)
+        self._check(self.lib.dvr_render_forward_gradients_ex(ci, settings, co, g, options, self._stream(stream)))
+
+    def render_adjoint(self, inputs: Inputs, color, termination_index, adj_color, adj: DvrAdjointOutputs,
+                       stream=None, options: DvrCallOptions = None):
+        self._validate(inputs, [("output_color", color, "float32"), ("terminationIndex", termination_index, "int32"),
+                                ("adj_color", adj_color, "float32")])
+        ci, co, ac = inputs.to_c(), make_outputs(color, termination_index), tensor_view(adj_color)
+        self._check(self.lib.dvr_render_adjoint_ex(ci, co, ac, adj, options, self._stream(stream)))
+
+    def workspace(self) -> "Workspace":
+        return Workspace(self)
+
+    def trim_scratch(self):
+        self._check(self.lib.dvr_trim_scratch())
+
+    def stat(self, name: str) -> int:
+        v = ctypes.c_int64()
+        self._check(self.lib.dvr_get_stat(name.encode(), ctypes.byref(v)))
+        return int(v.value)
+
+    def has_variant_pass(self, pass_id, filter_mode, camera_mode, tf_mode, blend_mode) -> bool:
+        return bool(self.lib.dvr_has_variant_pass(pass_id, filter_mode, camera_mode, tf_mode, blend_mode))
+
     def set_option(self, name: str, value: int):
         self._check(self.lib.dvr_set_option(name.encode(), int(value)))
 
@@ -385,10 +519,11 @@ class ProductLibrary(Library):
     def has_variant(self, filter_mode, camera_mode, tf_mode, blend_mode) -> bool:
         return bool(self.lib.dvr_has_variant(filter_mode, camera_mode, tf_mode, blend_mode))
 
-    def count_cell_visits(self, inputs: Inputs, termination_index, counts, stream: int = 0):
+    def count_cell_visits(self, inputs: Inputs, termination_index, counts, stream=None):
         """counts: device tensor of 2 int64 {N_samples, N_cells}, accumulated."""
+        self._validate(inputs, [("terminationIndex", termination_index, "int32")])
         ci, t = inputs.to_c(), tensor_view(termination_index)
-        self._check(self.lib.dvr_count_cell_visits(ci, t, counts.data_ptr(), stream))
+        self._check(self.lib.dvr_count_cell_visits(ci, t, counts.data_ptr(), self._stream(stream)))
 
     def check_inputs(self, inputs: Inputs):
         B, X, Y, Z = (ctypes.c_int32() for _ in range(4))
@@ -396,6 +531,49 @@ class ProductLibrary(Library):
         self._check(self.lib.dvr_check_inputs(ci, ctypes.byref(B), ctypes.byref(X), ctypes.byref(Y),
                                               ctypes.byref(Z)))
         return B.value, X.value, Y.value, Z.value
+
+
+PASS_FORWARD, PASS_FORWARD_GRADIENTS, PASS_ADJOINT = 0, 1, 2
+
+
+class Workspace:
+    """Persistent QUAD buffers of the library (include/dvr_b200.h DvrWorkspace): the volume copy is built once per
+    volume version, the gradient scratch is zeroed / folded once per accumulation scope."""
+
+    def __init__(self, lib: ProductLibrary):
+        self.lib = lib
+        self.handle = lib.lib.dvr_workspace_create()
+        if not self.handle:
+            raise DvrError(DVR_ERR_CUDA, lib.last_error())
+
+    def close(self):
+        if self.handle:
+            self.lib.lib.dvr_workspace_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_volume(self, volume, stream=None):
+        self.lib._check(self.lib.lib.dvr_workspace_set_volume(self.handle, tensor_view(volume, dtype="float32", what="volume"),
+                                                              self.lib._stream(stream)))
+
+    def invalidate(self):
+        self.lib._check(self.lib.lib.dvr_workspace_invalidate(self.handle))
+
+    def begin_volume_gradient(self, adj_volume, stream=None):
+        self.lib._check(self.lib.lib.dvr_workspace_begin_volume_gradient(
+            self.handle, tensor_view(adj_volume, dtype="float32", what="adj_volume"), self.lib._stream(stream)))
+
+    def end_volume_gradient(self, adj_volume, stream=None):
+        self.lib._check(self.lib.lib.dvr_workspace_end_volume_gradient(
+            self.handle, tensor_view(adj_volume, dtype="float32", what="adj_volume"), self.lib._stream(stream)))
+
+    def bytes(self) -> int:
+        return int(self.lib.lib.dvr_workspace_bytes(self.handle))
 
 
 def library_path() -> str:

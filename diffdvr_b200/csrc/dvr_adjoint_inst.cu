@@ -16,9 +16,9 @@ namespace dvr {
 template <int F, bool V, int A, bool R>
 static cudaError_t go(const RayInputs& in, const AdjointArgs& aa, dim3 grid, size_t smem, cudaStream_t s) {
   if constexpr (!V && A == kTfAccNone && !R) {
-    return cudaErrorInvalidValue;  // nothing to compute
+    return kErrNoInstance;  // nothing to compute
   } else if constexpr (DVR_TF == kTfIdentity && A == kTfAccSmem) {
-    return cudaErrorInvalidValue;  // the 2-entry identity table always lives in registers
+    return kErrNoInstance;  // the 2-entry identity table always lives in registers
   } else {
     return launch_kernel(k_adjoint<F, DVR_TF, DVR_BL, V, A, R>, grid, kThreads, smem, s, in, aa);
   }
@@ -33,7 +33,7 @@ static cudaError_t by_acc(int a, bool r, const RayInputs& in, const AdjointArgs&
     case kTfAccNone: return by_ray<F, V, kTfAccNone>(r, in, aa, g, sm, s);
     case kTfAccReg: return by_ray<F, V, kTfAccReg>(r, in, aa, g, sm, s);
     case kTfAccSmem: return by_ray<F, V, kTfAccSmem>(r, in, aa, g, sm, s);
-    default: return cudaErrorInvalidValue;
+    default: return kErrNoInstance;
   }
 }
 
@@ -48,7 +48,7 @@ cudaError_t DVR_NAME(DVR_TF, DVR_BL)(int filter, bool hasVol, int tfacc, bool ha
   if (filter == kFilterTrilinearQuad)
     return hasVol ? by_acc<kFilterTrilinearQuad, true>(tfacc, hasRay, in, aa, grid, smem, s)
                   : by_acc<kFilterTrilinearQuad, false>(tfacc, hasRay, in, aa, grid, smem, s);
-  return cudaErrorInvalidValue;
+  return kErrNoInstance;
 }
 
 }  // namespace dvr

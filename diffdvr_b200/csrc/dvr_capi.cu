@@ -8,6 +8,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 
 #include "../../include/dvr_b200.h"
@@ -19,10 +20,17 @@ namespace {
 using namespace dvr;
 
 thread_local std::string g_error;
-std::atomic<long long> g_launches{0};
-std::atomic<int> g_sync_mode{0};
-std::atomic<int> g_compat_stepsize{0};
-std::atomic<int> g_volume_layout{-1};
+thread_local int t_call_sync = 0;  // DvrCallOptions::sync of the call running on this thread
+std::atomic<long long> g_launches{0}, g_quad_builds{0}, g_quad_reuses{0}, g_quad_fallbacks{0}, g_folds{0};
+std::atomic<int> g_sync_mode{0};  // the one process-wide switch (Renderer::setCudaSyncMode)
+
+// per-call options resolved to plain values (DvrCallOptions, include/dvr_b200.h)
+struct CallCtx {
+  int layout = -1;
+  int compat = 0;
+  long long cap = 16ll << 30;
+  DvrWorkspace* ws = nullptr;
+};
 
 struct Fail {
   int code;
@@ -42,6 +50,7 @@ template <typename F>
 int guarded(F&& f) {
   try {
     f();
+    t_call_sync = 0;
     return DVR_OK;
   } catch (const Fail& e) {
     return e.code;
@@ -52,14 +61,35 @@ int guarded(F&& f) {
 }
 
 void cuda_check(cudaError_t e, const char* what) {
-  if (e == cudaErrorInvalidValue) fail(DVR_ERR_UNSUPPORTED, "%s: no precompiled kernel instance for this combination", what);
-  if (e != cudaSuccess) fail(DVR_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+  // kErrNoInstance is the launchers' own sentinel (dvr_launch.h); CUDA never returns it
+  if (e == kErrNoInstance) fail(DVR_ERR_UNSUPPORTED, "%s: no precompiled kernel instance for this combination", what);
+  if (e != cudaSuccess) {
+    cudaGetLastError();  // clear the sticky-less error state of the runtime
+    fail(DVR_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+  }
 }
 
 void after_launch(cudaError_t e, const char* what, cudaStream_t s) {
   cuda_check(e, what);
   g_launches.fetch_add(1, std::memory_order_relaxed);
-  if (g_sync_mode.load()) cuda_check(cudaStreamSynchronize(s), what);  // Renderer::setCudaSyncMode
+  if (g_sync_mode.load() || t_call_sync) cuda_check(cudaStreamSynchronize(s), what);  // Renderer::setCudaSyncMode
+}
+
+CallCtx resolve_options(const DvrCallOptions* o) {
+  CallCtx c;
+  t_call_sync = 0;
+  if (!o) return c;
+  if (o->struct_size < sizeof(DvrCallOptions))
+    fail(DVR_ERR_INVALID_ARGUMENT, "DvrCallOptions::struct_size is %u, expected %zu (use dvr_call_options_init)",
+         o->struct_size, sizeof(DvrCallOptions));
+  if (o->volume_layout < -1 || o->volume_layout > 1)
+    fail(DVR_ERR_INVALID_ARGUMENT, "volume_layout must be -1, 0 or 1, but is %d", o->volume_layout);
+  c.layout = o->volume_layout;
+  c.compat = o->compat_stepsize_overwrite != 0;
+  t_call_sync = o->sync != 0;
+  if (o->max_scratch_bytes > 0) c.cap = o->max_scratch_bytes;
+  c.ws = o->workspace;
+  return c;
 }
 
 // ---- shape checks, with the reference's wording (renderer/pytorch_utils.h:5-19) ---------------
@@ -368,10 +398,10 @@ void fill_gen_rays(const DvrTensor& viewport, float fovY, int W, int H, const Dv
   a.packed = W % 4 == 0 && packed(start) && packed(dir);
 }
 
-// ---- QUAD copy of the volume (RayInputs::quads) ------------------------------------------------
-// Stream-ordered scratch from the device's default memory pool (cudaMallocAsync / cudaFreeAsync): no
-// library-owned cache, safe with concurrent streams; the pool keeps the pages between calls once its
-// release threshold is raised. Option "volume_layout": 0 never, 1 always (trilinear), -1 automatic.
+// ---- QUAD buffers: copy of the volume (RayInputs::quads) and gradient scratch (AdjointArgs::gradQuads) --------
+// Per-call scratch is stream-ordered memory from a PRIVATE pool (one per device, created on first use): the
+// device's default pool -- which other cudaMallocAsync users share -- is left alone. The private pool keeps its
+// pages between calls (release threshold = max) until dvr_trim_scratch().
 struct QuadScratch {
   float4* ptr = nullptr;
   cudaStream_t stream = nullptr;
@@ -380,41 +410,166 @@ struct QuadScratch {
   }
 };
 
-void raise_pool_threshold() {
-  static std::atomic<unsigned long long> done{0};
+constexpr int kMaxDevices = 64;
+cudaMemPool_t g_pools[kMaxDevices] = {};
+std::mutex g_pool_mutex;
+
+cudaMemPool_t scratch_pool() {
   int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev >= 64) return;
-  if (done.load() & (1ull << dev)) return;
-  cudaMemPool_t pool;
-  if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return nullptr;
+  std::lock_guard<std::mutex> lock(g_pool_mutex);
+  if (!g_pools[dev]) {
+    cudaMemPoolProps props = {};
+    props.allocType = cudaMemAllocationTypePinned;
+    props.handleTypes = cudaMemHandleTypeNone;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = dev;
+    cudaMemPool_t pool = nullptr;
+    if (cudaMemPoolCreate(&pool, &props) != cudaSuccess) {
+      cudaGetLastError();
+      return nullptr;
+    }
     unsigned long long keep = ~0ull;
     cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    g_pools[dev] = pool;
   }
-  done.fetch_or(1ull << dev);
+  return g_pools[dev];
 }
 
-// returns the filter id to dispatch on (kFilterTrilinearQuad if the copy was built)
-int maybe_build_quads(int filter, Checked& c, QuadScratch& q, cudaStream_t s) {
-  if (filter != DVR_FILTER_TRILINEAR) return filter;
-  const int opt = g_volume_layout.load();
-  if (opt == 0) return filter;
-  const long long voxels = (long long)c.X * c.Y * c.Z;
-  const int nb = c.ri.volB == 0 ? 1 : c.B;
-  if (voxels >= (1ll << 31) || c.X < 2 || c.Y < 2 || c.Z < 2) return filter;
-  // automatic: the copy costs ~5 volume sweeps; worth it once the rays visit about as many cells as there are voxels
-  if (opt < 0 && (long long)c.B * c.W * c.H * 64 < voxels * nb) return filter;
-  raise_pool_threshold();
+bool scratch_alloc(QuadScratch& q, size_t bytes, cudaStream_t s) {
+  cudaMemPool_t pool = scratch_pool();
   void* p = nullptr;
-  if (cudaMallocAsync(&p, size_t(voxels) * nb * sizeof(float4), s) != cudaSuccess) {
-    cudaGetLastError();  // out of memory: sample the caller's tensor directly
-    return filter;
+  if (!pool || cudaMallocFromPoolAsync(&p, bytes, pool, s) != cudaSuccess) {
+    cudaGetLastError();  // out of memory: the caller takes the in-place path (counted)
+    return false;
   }
   q.ptr = static_cast<float4*>(p);
   q.stream = s;
-  after_launch(launch_build_quads(c.ri, nb, q.ptr, s), "dvr_build_quads", s);
-  c.ri.quads = q.ptr;
+  return true;
+}
+
+}  // namespace
+
+// Persistent QUAD buffers (include/dvr_b200.h "DvrWorkspace"). Plain cudaMalloc: long-lived, grown on demand.
+struct DvrWorkspace {
+  std::mutex m;
+  int device = 0;
+  // copy of the volume, valid for the tensor it was built from
+  float4* quads = nullptr;
+  size_t quadBytes = 0;
+  bool quadValid = false;
+  const void* volPtr = nullptr;
+  long long volSize[4] = {0, 0, 0, 0}, volStride[4] = {0, 0, 0, 0};
+  // gradient scratch
+  float4* grad = nullptr;
+  size_t gradBytes = 0;
+  bool accumulating = false;
+  const void* adjPtr = nullptr;  // adj_volume of the open accumulation scope
+  long long adjVoxels = 0;
+  int adjNb = 0;
+};
+
+namespace {
+
+bool ws_reserve(float4*& buf, size_t& have, size_t want) {
+  if (have >= want) return true;
+  if (buf) cudaFree(buf);  // synchronises: no kernel of an earlier call still reads it
+  buf = nullptr;
+  have = 0;
+  void* p = nullptr;
+  if (cudaMalloc(&p, want) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  buf = static_cast<float4*>(p);
+  have = want;
+  return true;
+}
+
+bool ws_volume_matches(const DvrWorkspace& w, const RayInputs& r, int nb) {
+  return w.quadValid && w.volPtr == r.volume && w.volSize[0] == nb && w.volSize[1] == r.X && w.volSize[2] == r.Y &&
+         w.volSize[3] == r.Z && w.volStride[0] == r.volB && w.volStride[1] == r.sx && w.volStride[2] == r.sy &&
+         w.volStride[3] == r.sz;
+}
+
+void ws_remember_volume(DvrWorkspace& w, const RayInputs& r, int nb) {
+  w.volPtr = r.volume;
+  w.volSize[0] = nb; w.volSize[1] = r.X; w.volSize[2] = r.Y; w.volSize[3] = r.Z;
+  w.volStride[0] = r.volB; w.volStride[1] = r.sx; w.volStride[2] = r.sy; w.volStride[3] = r.sz;
+  w.quadValid = true;
+}
+
+bool quad_eligible(const Checked& c) {
+  const long long voxels = (long long)c.X * c.Y * c.Z;
+  return voxels < (1ll << 31) && c.X >= 2 && c.Y >= 2 && c.Z >= 2;
+}
+
+// returns the filter id to dispatch on (kFilterTrilinearQuad if a QUAD copy of the volume serves this call)
+int maybe_build_quads(int filter, Checked& c, QuadScratch& q, const CallCtx& ctx, cudaStream_t s) {
+  if (filter != DVR_FILTER_TRILINEAR || ctx.layout == 0 || !quad_eligible(c)) return filter;
+  const long long voxels = (long long)c.X * c.Y * c.Z;
+  const int nb = c.ri.volB == 0 ? 1 : c.B;
+  const size_t bytes = size_t(voxels) * nb * sizeof(float4);
+  // automatic: the copy costs ~5 volume sweeps; worth it once the rays visit about as many cells as there are voxels
+  const bool worth = ctx.layout == 1 || (long long)c.B * c.W * c.H * 64 >= voxels * nb;
+  float4* quads = nullptr;
+  if (ctx.ws) {
+    DvrWorkspace& w = *ctx.ws;
+    std::lock_guard<std::mutex> lock(w.m);
+    if (ws_volume_matches(w, c.ri, nb)) {
+      g_quad_reuses.fetch_add(1, std::memory_order_relaxed);
+      quads = w.quads;  // free of charge: always used
+    } else {
+      if (!worth) return filter;
+      if ((long long)bytes > ctx.cap || !ws_reserve(w.quads, w.quadBytes, bytes)) {
+        w.quadValid = false;
+        g_quad_fallbacks.fetch_add(1, std::memory_order_relaxed);
+        return filter;
+      }
+      w.quadValid = false;
+      after_launch(launch_build_quads(c.ri, nb, w.quads, s), "dvr_build_quads", s);
+      g_quad_builds.fetch_add(1, std::memory_order_relaxed);
+      ws_remember_volume(w, c.ri, nb);
+      quads = w.quads;
+    }
+  } else {
+    if (!worth) return filter;
+    if ((long long)bytes > ctx.cap || !scratch_alloc(q, bytes, s)) {
+      g_quad_fallbacks.fetch_add(1, std::memory_order_relaxed);
+      return filter;
+    }
+    after_launch(launch_build_quads(c.ri, nb, q.ptr, s), "dvr_build_quads", s);
+    g_quad_builds.fetch_add(1, std::memory_order_relaxed);
+    quads = q.ptr;
+  }
+  c.ri.quads = quads;
   c.ri.quadB = nb == 1 ? 0 : voxels;
   return kFilterTrilinearQuad;
+}
+
+// (B)*X*Y*Z tensor -> the volume fields of RayInputs (shared by the workspace entry points)
+void volume_fields(const DvrTensor& t, const char* name, RayInputs& r, int& nb) {
+  check_dim(t, name, 4);
+  std::memset(&r, 0, sizeof(r));
+  r.X = int(t.size[1]); r.Y = int(t.size[2]); r.Z = int(t.size[3]);
+  if (r.X < 1 || r.Y < 1 || r.Z < 1 || t.size[0] < 1) fail(DVR_ERR_INVALID_ARGUMENT, "%s must not be empty", name);
+  long long span = 0;
+  for (int d = 1; d < 4; ++d) span += (t.size[d] - 1) * bstride(t, d);
+  if (span >= (1ll << 31) || t.size[1] >= (1 << 22) || t.size[2] >= (1 << 22) || t.size[3] >= (1 << 22))
+    fail(DVR_ERR_UNSUPPORTED, "one %s batch entry must span fewer than 2^31 elements", name);
+  if (t.size[0] > 65535) fail(DVR_ERR_UNSUPPORTED, "batch size %lld exceeds 65535", (long long)t.size[0]);
+  r.volume = static_cast<const float*>(t.ptr);
+  r.volB = bstride(t, 0);
+  r.sx = int(bstride(t, 1)); r.sy = int(bstride(t, 2)); r.sz = int(bstride(t, 3));
+  nb = int(t.size[0]);
+}
+
+// a spatial dimension of size > 1 with stride 0 (an expanded view): several voxels share one address, which
+// only the atomics of the in-place path accumulate correctly
+bool aliased_spatial_strides(const DvrTensor& t) {
+  for (int d = 1; d < 4; ++d)
+    if (t.size[d] > 1 && t.stride[d] == 0) return true;
+  return false;
 }
 
 }  // namespace
@@ -425,10 +580,9 @@ cudaError_t launch_adjoint(int filter, int tf, int blend, bool hasVol, int tfacc
                            const AdjointArgs& aa, dim3 grid, size_t smem, cudaStream_t s) {
 #define DVR_CASE(TF, BL) \
   if (tf == TF && blend == BL) return launch_adjoint_##TF##_##BL(filter, hasVol, tfacc, hasRay, in, aa, grid, smem, s);
-  DVR_CASE(0, 0) DVR_CASE(0, 1) DVR_CASE(1, 0) DVR_CASE(1, 1) DVR_CASE(2, 0) DVR_CASE(2, 1) DVR_CASE(3, 0)
-  DVR_CASE(3, 1) DVR_CASE(6, 0) DVR_CASE(6, 1)
+  DVR_FOR_EACH_ADJOINT_INSTANCE(DVR_CASE)
 #undef DVR_CASE
-  return cudaErrorInvalidValue;
+  return kErrNoInstance;
 }
 
 cudaError_t launch_forward_gradients(int filter, int tf, int blend, int chunk, bool hasPos, bool hasTf,
@@ -436,10 +590,9 @@ cudaError_t launch_forward_gradients(int filter, int tf, int blend, int chunk, b
                                      dim3 grid, size_t smem, cudaStream_t s) {
 #define DVR_CASE(TF, BL) \
   if (tf == TF && blend == BL) return launch_fwdgrad_##TF##_##BL(filter, chunk, hasPos, hasTf, in, out, ga, grid, smem, s);
-  DVR_CASE(0, 0) DVR_CASE(0, 1) DVR_CASE(1, 0) DVR_CASE(1, 1) DVR_CASE(2, 0) DVR_CASE(2, 1) DVR_CASE(3, 0)
-  DVR_CASE(3, 1)
+  DVR_FOR_EACH_FWDGRAD_INSTANCE(DVR_CASE)
 #undef DVR_CASE
-  return cudaErrorInvalidValue;
+  return kErrNoInstance;
 }
 
 }  // namespace dvr
@@ -460,8 +613,14 @@ int dvr_check_inputs(const DvrInputs* inputs, int32_t* B, int32_t* X, int32_t* Y
 }
 
 int dvr_render_forward(const DvrInputs* inputs, const DvrOutputs* outputs, void* stream) {
+  return dvr_render_forward_ex(inputs, outputs, nullptr, stream);
+}
+
+int dvr_render_forward_ex(const DvrInputs* inputs, const DvrOutputs* outputs, const DvrCallOptions* options,
+                          void* stream) {
   return guarded([&] {
     if (!inputs || !outputs) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    const CallCtx ctx = resolve_options(options);
     Checked c;
     check_inputs(*inputs, c);
     const ForwardOutputs fo = check_outputs(*outputs, c);
@@ -472,7 +631,7 @@ int dvr_render_forward(const DvrInputs* inputs, const DvrOutputs* outputs, void*
     }
     const size_t smem = check_smem(size_t(c.ri.R) * tf_row(inputs->tf_mode) * sizeof(float));
     QuadScratch quads;
-    const int filter = maybe_build_quads(inputs->volume_filter_mode, c, quads, s);
+    const int filter = maybe_build_quads(inputs->volume_filter_mode, c, quads, ctx, s);
     after_launch(launch_forward(filter, inputs->tf_mode, inputs->blend_mode, c.ri, fo,
                                 tile_grid(c), smem, s),
                  "dvr_render_forward", s);
@@ -481,8 +640,14 @@ int dvr_render_forward(const DvrInputs* inputs, const DvrOutputs* outputs, void*
 
 int dvr_render_adjoint(const DvrInputs* inputs, const DvrOutputs* fwd, const DvrTensor* adj_color,
                        const DvrAdjointOutputs* adj, void* stream) {
+  return dvr_render_adjoint_ex(inputs, fwd, adj_color, adj, nullptr, stream);
+}
+
+int dvr_render_adjoint_ex(const DvrInputs* inputs, const DvrOutputs* fwd, const DvrTensor* adj_color,
+                          const DvrAdjointOutputs* adj, const DvrCallOptions* options, void* stream) {
   return guarded([&] {
     if (!inputs || !fwd || !adj_color || !adj) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    const CallCtx ctx = resolve_options(options);
     Checked c;
     check_inputs(*inputs, c);
     // outputs of the forward pass (renderer.cpp:670-691) and adjoint colour (:693-701)
@@ -512,7 +677,7 @@ int dvr_render_adjoint(const DvrInputs* inputs, const DvrOutputs* fwd, const Dvr
     const bool hasVol = adj->has_volume_derivatives != 0, hasTf = adj->has_tf_derivatives != 0;
     const bool hasRay = aa.hasStep || aa.hasCam;
     if (!hasVol && !hasTf && !hasRay) fail(DVR_ERR_INVALID_ARGUMENT, "At least one adjoint variable must be activated!");
-    aa.compatStepOverwrite = g_compat_stepsize.load();
+    aa.compatStepOverwrite = ctx.compat;
     aa.sameStrides = hasVol && aa.avx == c.ri.sx && aa.avy == c.ri.sy && aa.avz == c.ri.sz;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (preshaded) {
@@ -530,36 +695,63 @@ int dvr_render_adjoint(const DvrInputs* inputs, const DvrOutputs* fwd, const Dvr
     const size_t smem =
         check_smem((size_t((c.ri.R * tf_row(tf) + 3) & ~3) + size_t(ntab) * entries) * sizeof(float));
     QuadScratch quads, gradQuads;
-    int filter = maybe_build_quads(inputs->volume_filter_mode, c, quads, s);
+    int filter = maybe_build_quads(inputs->volume_filter_mode, c, quads, ctx, s);
     int ng = 0;
+    bool fold = false;
     if (filter == kFilterTrilinearQuad && hasVol) {
       // gradient scratch in the same layout: 2 x red.v4 per cell instead of 8 scalar REDs, folded afterwards
       const long long voxels = (long long)c.X * c.Y * c.Z;
       ng = aa.avB == 0 ? 1 : c.B;
-      void* p = nullptr;
       const size_t bytes = size_t(voxels) * ng * sizeof(float4);
-      if (cudaMallocAsync(&p, bytes, s) == cudaSuccess) {
-        gradQuads.ptr = static_cast<float4*>(p);
-        gradQuads.stream = s;
-        cuda_check(cudaMemsetAsync(p, 0, bytes, s), "dvr_render_adjoint");
-        aa.gradQuads = gradQuads.ptr;
+      float4* grad = nullptr;
+      if (aliased_spatial_strides(adj->adj_volume) || (long long)bytes > ctx.cap) {
+        // expanded adj_volume views need the atomics of the in-place path (a fold would lose updates)
+      } else if (ctx.ws) {
+        DvrWorkspace& w = *ctx.ws;
+        std::lock_guard<std::mutex> lock(w.m);
+        if (w.accumulating && w.adjPtr == adj->adj_volume.ptr && w.adjVoxels == voxels && w.adjNb == ng) {
+          grad = w.grad;  // open accumulation scope: zeroed by begin_volume_gradient, folded by end_volume_gradient
+        } else if (!w.accumulating && ws_reserve(w.grad, w.gradBytes, bytes)) {
+          cuda_check(cudaMemsetAsync(w.grad, 0, bytes, s), "dvr_render_adjoint");
+          grad = w.grad;
+          fold = true;
+        }
+      }
+      if (!grad && !(ctx.ws && ctx.ws->accumulating) && !aliased_spatial_strides(adj->adj_volume) &&
+          (long long)bytes <= ctx.cap && scratch_alloc(gradQuads, bytes, s)) {
+        cuda_check(cudaMemsetAsync(gradQuads.ptr, 0, bytes, s), "dvr_render_adjoint");
+        grad = gradQuads.ptr;
+        fold = true;
+      }
+      if (grad) {
+        aa.gradQuads = grad;
         aa.gradQuadB = ng == 1 ? 0 : voxels;
       } else {
-        cudaGetLastError();
-        filter = inputs->volume_filter_mode;  // not enough memory for the scratch: in-place path
+        g_quad_fallbacks.fetch_add(1, std::memory_order_relaxed);
+        filter = inputs->volume_filter_mode;  // no scratch: the in-place path accumulates straight into adj_volume
       }
     }
     after_launch(launch_adjoint(filter, tf, inputs->blend_mode, hasVol, tfacc, hasRay, c.ri, aa,
                                 tile_grid(c), smem, s),
                  "dvr_render_adjoint", s);
-    if (aa.gradQuads) after_launch(launch_fold_quads(c.ri, aa, ng, s), "dvr_fold_quads", s);
+    if (fold) {
+      after_launch(launch_fold_quads(c.ri, aa, ng, s), "dvr_fold_quads", s);
+      g_folds.fetch_add(1, std::memory_order_relaxed);
+    }
   });
 }
 
 int dvr_render_forward_gradients(const DvrInputs* inputs, const DvrForwardDifferencesSettings* st,
                                  const DvrOutputs* outputs, const DvrTensor* gradients_out, void* stream) {
+  return dvr_render_forward_gradients_ex(inputs, st, outputs, gradients_out, nullptr, stream);
+}
+
+int dvr_render_forward_gradients_ex(const DvrInputs* inputs, const DvrForwardDifferencesSettings* st,
+                                    const DvrOutputs* outputs, const DvrTensor* gradients_out,
+                                    const DvrCallOptions* options, void* stream) {
   return guarded([&] {
     if (!inputs || !st || !outputs || !gradients_out) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    const CallCtx ctx = resolve_options(options);
     Checked c;
     check_inputs(*inputs, c);
     if (st->D <= 0) fail(DVR_ERR_INVALID_ARGUMENT, "number of derivatives must be positive");
@@ -600,7 +792,7 @@ int dvr_render_forward_gradients(const DvrInputs* inputs, const DvrForwardDiffer
     const size_t smem = check_smem(size_t(((c.ri.R * tf_row(tf) + 3) & ~3) + c.ri.R * tf_row(tf)) * sizeof(float));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     QuadScratch quads;  // one QUAD copy of the volume serves all passes
-    const int filter = maybe_build_quads(inputs->volume_filter_mode, c, quads, s);
+    const int filter = maybe_build_quads(inputs->volume_filter_mode, c, quads, ctx, s);
     if (!hasTf) {
       // ray / stepsize tangents only: the slots are a linear map of <= 7 input tangents carried per input, ONE
       // marching pass for any D (k_forward_gradients_inputs)
@@ -885,6 +1077,7 @@ int dvr_volume_from_raw(const void* raw, int32_t dtype, const DvrTensor* volume_
     if (dtype < 0 || dtype > 2) fail(DVR_ERR_INVALID_ARGUMENT, "unknown .cvol data type %d", dtype);
     RawVolumeArgs a{};
     volume_dims(*volume_out, "volume", a.X, a.Y, a.Z);
+    if (a.Y > 65535) fail(DVR_ERR_UNSUPPORTED, "volume conversion supports Y <= 65535, but Y is %d", a.Y);
     a.raw = const_cast<void*>(raw);
     a.vol = static_cast<float*>(volume_out->ptr);
     a.sx = volume_out->stride[1]; a.sy = volume_out->stride[2]; a.sz = volume_out->stride[3];
@@ -898,6 +1091,7 @@ int dvr_volume_to_raw(const DvrTensor* volume, float* raw_out, void* stream) {
     if (!raw_out || !volume) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
     RawVolumeArgs a{};
     volume_dims(*volume, "volume", a.X, a.Y, a.Z);
+    if (a.Y > 65535) fail(DVR_ERR_UNSUPPORTED, "volume conversion supports Y <= 65535, but Y is %d", a.Y);
     a.raw = raw_out;
     a.vol = static_cast<float*>(volume->ptr);
     a.sx = volume->stride[1]; a.sy = volume->stride[2]; a.sz = volume->stride[3];
@@ -941,34 +1135,166 @@ int dvr_count_cell_visits(const DvrInputs* inputs, const DvrTensor* termination_
   });
 }
 
+int dvr_has_variant_pass(int32_t pass, int32_t filter, int32_t camera, int32_t tf, int32_t blend) {
+  if (camera < 0 || camera > 2) return 0;  // the camera mode is a run-time switch inside every instance
+  if (blend != DVR_BLEND_BEER_LAMBERT && blend != DVR_BLEND_ALPHA) return 0;
+  if (filter == DVR_FILTER_PRESHADED || tf == DVR_TF_PRESHADED)  // only valid together; dvr_preshaded.cu, no forward-mode
+    return filter == DVR_FILTER_PRESHADED && tf == DVR_TF_PRESHADED && pass != DVR_PASS_FORWARD_GRADIENTS &&
+           (pass == DVR_PASS_FORWARD || pass == DVR_PASS_ADJOINT);
+  if (filter != DVR_FILTER_NEAREST && filter != DVR_FILTER_TRILINEAR) return 0;
+  // membership in the SAME lists that declare and dispatch the instance translation units (dvr_launch.h)
+#define DVR_MATCH(TF, BL) if (tf == TF && blend == BL) return 1;
+  switch (pass) {
+    case DVR_PASS_FORWARD: { DVR_FOR_EACH_FORWARD_INSTANCE(DVR_MATCH) } break;
+    case DVR_PASS_FORWARD_GRADIENTS: { DVR_FOR_EACH_FWDGRAD_INSTANCE(DVR_MATCH) } break;
+    case DVR_PASS_ADJOINT: { DVR_FOR_EACH_ADJOINT_INSTANCE(DVR_MATCH) } break;
+    default: break;
+  }
+#undef DVR_MATCH
+  return 0;
+}
+
 int dvr_has_variant(int32_t filter, int32_t camera, int32_t tf, int32_t blend) {
-  const bool c = camera >= 0 && camera <= 2;
-  if (filter == DVR_FILTER_PRESHADED || tf == DVR_TF_PRESHADED)  // only valid together
-    return filter == DVR_FILTER_PRESHADED && tf == DVR_TF_PRESHADED && c &&
-           (blend == DVR_BLEND_BEER_LAMBERT || blend == DVR_BLEND_ALPHA);
-  const bool f = filter == DVR_FILTER_NEAREST || filter == DVR_FILTER_TRILINEAR;
-  const bool t = tf == DVR_TF_IDENTITY || tf == DVR_TF_TEXTURE || tf == DVR_TF_LINEAR || tf == DVR_TF_GAUSSIAN ||
-                 tf == DVR_TF_GAUSSIAN_LOG;
-  const bool b = blend == DVR_BLEND_BEER_LAMBERT || blend == DVR_BLEND_ALPHA;
-  return f && c && t && b;
+  return dvr_has_variant_pass(DVR_PASS_FORWARD, filter, camera, tf, blend) &&
+         dvr_has_variant_pass(DVR_PASS_ADJOINT, filter, camera, tf, blend);
 }
 
 int dvr_set_option(const char* name, int32_t value) {
   if (!name) return DVR_ERR_INVALID_ARGUMENT;
   if (!std::strcmp(name, "sync_mode")) { g_sync_mode = value; return DVR_OK; }
-  if (!std::strcmp(name, "compat_stepsize_overwrite")) { g_compat_stepsize = value; return DVR_OK; }
-  if (!std::strcmp(name, "volume_layout")) { g_volume_layout = value; return DVR_OK; }
-  g_error = std::string("unknown option '") + name + "'";
+  g_error = std::string("unknown option '") + name + "' (results-changing options are per call: DvrCallOptions)";
   return DVR_ERR_INVALID_ARGUMENT;
 }
 
 int dvr_get_option(const char* name, int32_t* value) {
   if (!name || !value) return DVR_ERR_INVALID_ARGUMENT;
   if (!std::strcmp(name, "sync_mode")) { *value = g_sync_mode; return DVR_OK; }
-  if (!std::strcmp(name, "compat_stepsize_overwrite")) { *value = g_compat_stepsize; return DVR_OK; }
-  if (!std::strcmp(name, "volume_layout")) { *value = g_volume_layout; return DVR_OK; }
   g_error = std::string("unknown option '") + name + "'";
   return DVR_ERR_INVALID_ARGUMENT;
+}
+
+int dvr_get_stat(const char* name, int64_t* value) {
+  if (!name || !value) return DVR_ERR_INVALID_ARGUMENT;
+  if (!std::strcmp(name, "launches")) { *value = g_launches.load(); return DVR_OK; }
+  if (!std::strcmp(name, "quad_builds")) { *value = g_quad_builds.load(); return DVR_OK; }
+  if (!std::strcmp(name, "quad_reuses")) { *value = g_quad_reuses.load(); return DVR_OK; }
+  if (!std::strcmp(name, "quad_fallbacks")) { *value = g_quad_fallbacks.load(); return DVR_OK; }
+  if (!std::strcmp(name, "folds")) { *value = g_folds.load(); return DVR_OK; }
+  g_error = std::string("unknown counter '") + name + "'";
+  return DVR_ERR_INVALID_ARGUMENT;
+}
+
+void dvr_call_options_init(DvrCallOptions* o) {
+  if (!o) return;
+  std::memset(o, 0, sizeof(*o));
+  o->struct_size = sizeof(DvrCallOptions);
+  o->volume_layout = -1;
+}
+
+DvrWorkspace* dvr_workspace_create(void) {
+  DvrWorkspace* w = new (std::nothrow) DvrWorkspace();
+  if (!w || cudaGetDevice(&w->device) != cudaSuccess) {
+    g_error = "dvr_workspace_create: no CUDA device";
+    delete w;
+    return nullptr;
+  }
+  return w;
+}
+
+void dvr_workspace_destroy(DvrWorkspace* w) {
+  if (!w) return;
+  if (w->quads) cudaFree(w->quads);
+  if (w->grad) cudaFree(w->grad);
+  delete w;
+}
+
+int64_t dvr_workspace_bytes(const DvrWorkspace* w) { return w ? int64_t(w->quadBytes + w->gradBytes) : 0; }
+
+int dvr_workspace_invalidate(DvrWorkspace* w) {
+  return guarded([&] {
+    if (!w) fail(DVR_ERR_INVALID_ARGUMENT, "NULL workspace");
+    std::lock_guard<std::mutex> lock(w->m);
+    w->quadValid = false;
+  });
+}
+
+int dvr_workspace_set_volume(DvrWorkspace* w, const DvrTensor* volume, void* stream) {
+  return guarded([&] {
+    if (!w || !volume) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    RayInputs r;
+    int nb = 1;
+    volume_fields(*volume, "volume", r, nb);
+    if (r.X < 2 || r.Y < 2 || r.Z < 2 || (long long)r.X * r.Y * r.Z >= (1ll << 31))
+      fail(DVR_ERR_UNSUPPORTED, "the QUAD layout needs 2 <= X, Y, Z and fewer than 2^31 voxels");
+    if (r.volB == 0) nb = 1;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    std::lock_guard<std::mutex> lock(w->m);
+    w->quadValid = false;
+    if (!ws_reserve(w->quads, w->quadBytes, size_t(r.X) * r.Y * r.Z * nb * sizeof(float4)))
+      fail(DVR_ERR_CUDA, "dvr_workspace_set_volume: out of device memory for the QUAD copy");
+    after_launch(launch_build_quads(r, nb, w->quads, s), "dvr_build_quads", s);
+    g_quad_builds.fetch_add(1, std::memory_order_relaxed);
+    ws_remember_volume(*w, r, nb);
+  });
+}
+
+int dvr_workspace_begin_volume_gradient(DvrWorkspace* w, const DvrTensor* adj_volume, void* stream) {
+  return guarded([&] {
+    if (!w || !adj_volume) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    RayInputs r;
+    int nb = 1;
+    volume_fields(*adj_volume, "adj_volume", r, nb);
+    if (r.volB == 0) nb = 1;
+    if (aliased_spatial_strides(*adj_volume))
+      fail(DVR_ERR_UNSUPPORTED, "adj_volume views with stride-0 spatial dimensions accumulate in place only");
+    if (r.X < 2 || r.Y < 2 || r.Z < 2 || (long long)r.X * r.Y * r.Z >= (1ll << 31))
+      fail(DVR_ERR_UNSUPPORTED, "the QUAD layout needs 2 <= X, Y, Z and fewer than 2^31 voxels");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    std::lock_guard<std::mutex> lock(w->m);
+    if (w->accumulating) fail(DVR_ERR_INVALID_ARGUMENT, "a volume-gradient scope is already open on this workspace");
+    const long long voxels = (long long)r.X * r.Y * r.Z;
+    const size_t bytes = size_t(voxels) * nb * sizeof(float4);
+    if (!ws_reserve(w->grad, w->gradBytes, bytes))
+      fail(DVR_ERR_CUDA, "dvr_workspace_begin_volume_gradient: out of device memory for the gradient scratch");
+    cuda_check(cudaMemsetAsync(w->grad, 0, bytes, s), "dvr_workspace_begin_volume_gradient");
+    w->accumulating = true;
+    w->adjPtr = adj_volume->ptr;
+    w->adjVoxels = voxels;
+    w->adjNb = nb;
+  });
+}
+
+int dvr_workspace_end_volume_gradient(DvrWorkspace* w, const DvrTensor* adj_volume, void* stream) {
+  return guarded([&] {
+    if (!w || !adj_volume) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    RayInputs r;
+    int nb = 1;
+    volume_fields(*adj_volume, "adj_volume", r, nb);
+    if (r.volB == 0) nb = 1;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    std::lock_guard<std::mutex> lock(w->m);
+    if (!w->accumulating) fail(DVR_ERR_INVALID_ARGUMENT, "no volume-gradient scope is open on this workspace");
+    if (w->adjPtr != adj_volume->ptr || w->adjVoxels != (long long)r.X * r.Y * r.Z || w->adjNb != nb)
+      fail(DVR_ERR_INVALID_ARGUMENT, "adj_volume differs from the tensor the scope was opened with");
+    AdjointArgs aa;
+    std::memset(&aa, 0, sizeof(aa));
+    aa.adjVolume = static_cast<float*>(adj_volume->ptr);
+    aa.avB = r.volB; aa.avx = r.sx; aa.avy = r.sy; aa.avz = r.sz;
+    aa.gradQuads = w->grad;
+    aa.gradQuadB = nb == 1 ? 0 : w->adjVoxels;
+    w->accumulating = false;
+    after_launch(launch_fold_quads(r, aa, nb, s), "dvr_fold_quads", s);
+    g_folds.fetch_add(1, std::memory_order_relaxed);
+  });
+}
+
+int dvr_trim_scratch(void) {
+  return guarded([&] {
+    int dev = 0;
+    cuda_check(cudaGetDevice(&dev), "dvr_trim_scratch");
+    std::lock_guard<std::mutex> lock(g_pool_mutex);
+    if (dev >= 0 && dev < kMaxDevices && g_pools[dev]) cuda_check(cudaMemPoolTrimTo(g_pools[dev], 0), "dvr_trim_scratch");
+  });
 }
 
 int dvr_device_synchronize(void) {

@@ -9,14 +9,12 @@ namespace dvr {
 template <int F, int B>
 static cudaError_t by_tf(int tf, const RayInputs& in, const ForwardOutputs& out, dim3 grid, size_t smem,
                          cudaStream_t s) {
-  switch (tf) {
-    case kTfIdentity: return launch_kernel(k_forward<F, kTfIdentity, B>, grid, kThreads, smem, s, in, out);
-    case kTfTexture: return launch_kernel(k_forward<F, kTfTexture, B>, grid, kThreads, smem, s, in, out);
-    case kTfLinear: return launch_kernel(k_forward<F, kTfLinear, B>, grid, kThreads, smem, s, in, out);
-    case kTfGaussian: return launch_kernel(k_forward<F, kTfGaussian, B>, grid, kThreads, smem, s, in, out);
-    case kTfGaussianLog: return launch_kernel(k_forward<F, kTfGaussianLog, B>, grid, kThreads, smem, s, in, out);
-    default: return cudaErrorInvalidValue;
-  }
+  // one case per (tf, blend) pair of DVR_FOR_EACH_FORWARD_INSTANCE (dvr_launch.h)
+#define DVR_CASE(TF, BL) \
+  if (tf == TF && B == BL) return launch_kernel(k_forward<F, TF, BL>, grid, kThreads, smem, s, in, out);
+  DVR_FOR_EACH_FORWARD_INSTANCE(DVR_CASE)
+#undef DVR_CASE
+  return kErrNoInstance;
 }
 
 cudaError_t launch_forward(int filter, int tf, int blend, const RayInputs& in, const ForwardOutputs& out,
@@ -27,7 +25,7 @@ cudaError_t launch_forward(int filter, int tf, int blend, const RayInputs& in, c
   if (filter == kFilterTrilinear && blend == kBlendAlpha) return by_tf<kFilterTrilinear, kBlendAlpha>(tf, in, out, grid, smem, s);
   if (filter == kFilterTrilinearQuad && blend == kBlendBeer) return by_tf<kFilterTrilinearQuad, kBlendBeer>(tf, in, out, grid, smem, s);
   if (filter == kFilterTrilinearQuad && blend == kBlendAlpha) return by_tf<kFilterTrilinearQuad, kBlendAlpha>(tf, in, out, grid, smem, s);
-  return cudaErrorInvalidValue;
+  return kErrNoInstance;
 }
 
 }  // namespace dvr

@@ -17,19 +17,19 @@ static cudaError_t by_flags(bool p, bool t, const RayInputs& in, const ForwardOu
   if (p && t) return launch_kernel(k_forward_gradients<F, DVR_TF, DVR_BL, N, true, true>, g, kThreads, sm, s, in, out, ga);
   // ray / stepsize tangents without TF tangents go through k_forward_gradients_inputs (chunk 0)
   if (t) return launch_kernel(k_forward_gradients<F, DVR_TF, DVR_BL, N, false, true>, g, kThreads, sm, s, in, out, ga);
-  return cudaErrorInvalidValue;
+  return kErrNoInstance;
 }
 template <int F>
 static cudaError_t by_chunk(int n, bool p, bool t, const RayInputs& in, const ForwardOutputs& out,
                             const ForwardGradArgs& ga, dim3 g, size_t sm, cudaStream_t s) {
   switch (n) {
     case 0:  // input-major single pass: ray / stepsize tangents only (k_forward_gradients_inputs)
-      if (!p || t) return cudaErrorInvalidValue;
+      if (!p || t) return kErrNoInstance;
       return launch_kernel(k_forward_gradients_inputs<F, DVR_TF, DVR_BL>, g, kThreads, sm, s, in, out, ga);
     case 1: return by_flags<F, 1>(p, t, in, out, ga, g, sm, s);
     case 6: return by_flags<F, 6>(p, t, in, out, ga, g, sm, s);
     case 8: return by_flags<F, 8>(p, t, in, out, ga, g, sm, s);
-    default: return cudaErrorInvalidValue;
+    default: return kErrNoInstance;
   }
 }
 
@@ -39,7 +39,7 @@ cudaError_t DVR_NAME(DVR_TF, DVR_BL)(int filter, int chunk, bool hasPos, bool ha
   if (filter == kFilterNearest) return by_chunk<kFilterNearest>(chunk, hasPos, hasTf, in, out, ga, grid, smem, s);
   if (filter == kFilterTrilinear) return by_chunk<kFilterTrilinear>(chunk, hasPos, hasTf, in, out, ga, grid, smem, s);
   if (filter == kFilterTrilinearQuad) return by_chunk<kFilterTrilinearQuad>(chunk, hasPos, hasTf, in, out, ga, grid, smem, s);
-  return cudaErrorInvalidValue;
+  return kErrNoInstance;
 }
 
 }  // namespace dvr

@@ -6,9 +6,20 @@
 #include <cuda_runtime.h>
 #include "dvr_params.h"
 
+// The (tf, blend) pairs that have instance translation units: ONE list per pass declares the launchers below, drives
+// the dispatch switches of dvr_capi.cu and answers dvr_has_variant_pass(), so the three cannot drift apart (a pair
+// missing from the Makefile's TFS_* lists fails at link time). TF ids: 0 Identity, 1 Texture, 2 Linear, 3 Gaussian,
+// 6 GaussianLog (no forward-mode: its forward derivatives are deleted in the reference too, renderer_tf.cuh:692-702).
+#define DVR_FOR_EACH_ADJOINT_INSTANCE(X) X(0, 0) X(0, 1) X(1, 0) X(1, 1) X(2, 0) X(2, 1) X(3, 0) X(3, 1) X(6, 0) X(6, 1)
+#define DVR_FOR_EACH_FWDGRAD_INSTANCE(X) X(0, 0) X(0, 1) X(1, 0) X(1, 1) X(2, 0) X(2, 1) X(3, 0) X(3, 1)
+// the plain forward kernels live in one translation unit (dvr_forward.cu) that switches over the same TF set
+#define DVR_FOR_EACH_FORWARD_INSTANCE(X) DVR_FOR_EACH_ADJOINT_INSTANCE(X)
+
 namespace dvr {
 
-// returns cudaErrorInvalidValue if the combination has no instance
+// the launchers' own "no precompiled instance for this combination" (never returned by the CUDA runtime)
+constexpr cudaError_t kErrNoInstance = static_cast<cudaError_t>(20001);
+
 cudaError_t launch_forward(int filter, int tf, int blend, const RayInputs& in, const ForwardOutputs& out,
                            dim3 grid, size_t smem, cudaStream_t stream);
 
@@ -58,16 +69,14 @@ cudaError_t launch_downsample_volume(const DownsampleArgs& a, cudaStream_t strea
   cudaError_t launch_adjoint_##TF##_##BL(int filter, bool hasVol, int tfacc, bool hasRay,             \
                                          const RayInputs& in, const AdjointArgs& aa, dim3 grid,       \
                                          size_t smem, cudaStream_t stream);
-DVR_DECL_ADJ(0, 0) DVR_DECL_ADJ(0, 1) DVR_DECL_ADJ(1, 0) DVR_DECL_ADJ(1, 1) DVR_DECL_ADJ(2, 0)
-DVR_DECL_ADJ(2, 1) DVR_DECL_ADJ(3, 0) DVR_DECL_ADJ(3, 1) DVR_DECL_ADJ(6, 0) DVR_DECL_ADJ(6, 1)
+DVR_FOR_EACH_ADJOINT_INSTANCE(DVR_DECL_ADJ)
 #undef DVR_DECL_ADJ
 #define DVR_DECL_FG(TF, BL)                                                                           \
   cudaError_t launch_fwdgrad_##TF##_##BL(int filter, int chunk, bool hasPos, bool hasTf,              \
                                          const RayInputs& in, const ForwardOutputs& out,              \
                                          const ForwardGradArgs& ga, dim3 grid, size_t smem,           \
                                          cudaStream_t stream);
-DVR_DECL_FG(0, 0) DVR_DECL_FG(0, 1) DVR_DECL_FG(1, 0) DVR_DECL_FG(1, 1) DVR_DECL_FG(2, 0)
-DVR_DECL_FG(2, 1) DVR_DECL_FG(3, 0) DVR_DECL_FG(3, 1)
+DVR_FOR_EACH_FWDGRAD_INSTANCE(DVR_DECL_FG)
 #undef DVR_DECL_FG
 
 template <typename K, typename... Args>

@@ -201,7 +201,7 @@ cudaError_t launch_forward_preshaded(int blend, const RayInputs& in, const Forwa
                                      cudaStream_t s) {
   if (blend == kBlendBeer) return launch_kernel(k_forward_preshaded<kBlendBeer>, grid, kThreads, 0, s, in, out);
   if (blend == kBlendAlpha) return launch_kernel(k_forward_preshaded<kBlendAlpha>, grid, kThreads, 0, s, in, out);
-  return cudaErrorInvalidValue;
+  return kErrNoInstance;
 }
 
 template <int BLEND>
@@ -210,14 +210,14 @@ static cudaError_t adj_by_flags(bool hasVol, bool hasRay, const RayInputs& in, c
   if (hasVol && hasRay) return launch_kernel(k_adjoint_preshaded<BLEND, true, true>, grid, kThreads, 0, s, in, aa);
   if (hasVol) return launch_kernel(k_adjoint_preshaded<BLEND, true, false>, grid, kThreads, 0, s, in, aa);
   if (hasRay) return launch_kernel(k_adjoint_preshaded<BLEND, false, true>, grid, kThreads, 0, s, in, aa);
-  return cudaErrorInvalidValue;
+  return kErrNoInstance;
 }
 
 cudaError_t launch_adjoint_preshaded(int blend, bool hasVol, bool hasRay, const RayInputs& in, const AdjointArgs& aa,
                                      dim3 grid, cudaStream_t s) {
   if (blend == kBlendBeer) return adj_by_flags<kBlendBeer>(hasVol, hasRay, in, aa, grid, s);
   if (blend == kBlendAlpha) return adj_by_flags<kBlendAlpha>(hasVol, hasRay, in, aa, grid, s);
-  return cudaErrorInvalidValue;
+  return kErrNoInstance;
 }
 
 }  // namespace dvr

@@ -55,7 +55,7 @@ cudaError_t launch_preshade(int tf, bool adjoint, const RayInputs& in, const Pre
     case kTfLinear: return go<kTfLinear>(adjoint, in, a, smem, s);
     case kTfGaussian: return go<kTfGaussian>(adjoint, in, a, smem, s);
     case kTfGaussianLog: return go<kTfGaussianLog>(adjoint, in, a, smem, s);
-    default: return cudaErrorInvalidValue;
+    default: return kErrNoInstance;
   }
 }
 

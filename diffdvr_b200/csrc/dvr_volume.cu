@@ -198,7 +198,7 @@ cudaError_t launch_volume_raw(int dtype, bool toRaw, const RawVolumeArgs& a, cud
     case 0: return launch_kernel(k_volume_raw<unsigned char, false>, grid, block, 0, s, a);
     case 1: return launch_kernel(k_volume_raw<unsigned short, false>, grid, block, 0, s, a);
     case 2: return launch_kernel(k_volume_raw<float, false>, grid, block, 0, s, a);
-    default: return cudaErrorInvalidValue;
+    default: return kErrNoInstance;
   }
 }
 

@@ -77,6 +77,12 @@ PYBIND11_MODULE(pyrenderer, m) {
         py::doc("library option of include/dvr_b200.h, e.g. 'compat_stepsize_overwrite'"));
   m.def("get_option", &Renderer::getOption, py::arg("name"));
   m.def("launch_count", &Renderer::launchCount, py::doc("number of CUDA kernels launched by the library so far"));
+  m.def("stat", &Renderer::stat, py::arg("name"),
+        py::doc("library counters since load: launches, quad_builds, quad_reuses, quad_fallbacks, folds"));
+  m.def("has_variant_pass", [](int pass, kernel::VolumeFilterMode f, kernel::CameraMode c, kernel::TFMode t, kernel::BlendMode b) {
+    return dvr_has_variant_pass(pass, int(f), int(c), int(t), int(b)) != 0;
+  }, py::arg("pass_id"), py::arg("filter"), py::arg("camera"), py::arg("tf"), py::arg("blend"),
+        py::doc("pass_id: 0 forward, 1 forward-mode, 2 adjoint"));
   m.def("has_variant", [](kernel::VolumeFilterMode f, kernel::CameraMode c, kernel::TFMode t, kernel::BlendMode b) {
     return dvr_has_variant(int(f), int(c), int(t), int(b)) != 0;
   }, py::doc("True iff a precompiled kernel instance exists for this combination"));

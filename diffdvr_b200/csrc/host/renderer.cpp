@@ -8,6 +8,8 @@
 #include <c10/cuda/CUDAGuard.h>
 #include <c10/cuda/CUDAStream.h>
 
+#include <atomic>
+#include <mutex>
 #include <stdexcept>
 
 #include "../../../include/dvr_b200.h"
@@ -167,6 +169,74 @@ DvrAdjointOutputs to_c(const AdjointOutputsHost& a, const torch::Device& dev) {
 
 void* current_stream(const torch::Device& dev) { return c10::cuda::getCurrentCUDAStream(dev.index()).stream(); }
 
+// ---- host-layer options and the volume cache --------------------------------------------------------------------
+// The C-ABI is reentrant (options travel per call); this class is, like the reference's, a static facade with
+// process-wide settings (Renderer::setCudaSyncMode & co), so its defaults live here and are passed per call.
+std::atomic<int> g_compat_stepsize{0}, g_volume_layout{-1}, g_volume_cache{1};
+
+// One workspace per device, keyed on the volume TENSOR: (data_ptr, sizes, strides) are checked by the library,
+// the contents by torch's version counter (every in-place operation bumps it). The cache holds a handle of the
+// tensor, so its address cannot be recycled for another tensor while the entry lives. Writes that bypass the
+// version counter (raw kernels, .data) need Renderer::setOption("volume_cache", 0) or cleanupCuda().
+struct VolumeCache {
+  std::mutex m;
+  DvrWorkspace* ws = nullptr;
+  torch::Tensor volume;
+  uint32_t version = 0;
+  void* stream = nullptr;
+};
+constexpr int kMaxDevices = 64;
+VolumeCache g_cache[kMaxDevices];
+
+struct CallOptions {
+  DvrCallOptions o;
+  std::unique_lock<std::mutex> lock;  // held while a cached workspace is in use by this call
+};
+
+void fill_options(CallOptions& c, const RendererInputsHost& in, const torch::Device& dev, void* stream) {
+  dvr_call_options_init(&c.o);
+  c.o.volume_layout = g_volume_layout.load();
+  c.o.compat_stepsize_overwrite = g_compat_stepsize.load();
+  if (!g_volume_cache.load() || c.o.volume_layout == 0 || in.volumeFilterMode != kernel::FilterTrilinear) return;
+  const int d = dev.index();
+  if (d < 0 || d >= kMaxDevices) return;
+  VolumeCache& vc = g_cache[d];
+  c.lock = std::unique_lock<std::mutex>(vc.m);
+  uint32_t version = 0;
+  try {
+    version = in.volume._version();
+  } catch (const c10::Error&) {  // inference tensors carry no version counter: do not cache them
+    c.lock.unlock();
+    return;
+  }
+  if (!vc.ws) vc.ws = dvr_workspace_create();
+  if (!vc.ws) {
+    c.lock.unlock();
+    return;
+  }
+  const bool same = vc.volume.defined() && vc.volume.is_same(in.volume) && vc.version == version;
+  if (same && vc.stream != stream) {  // the copy was built on another stream: stay off it (no cross-stream ordering)
+    c.lock.unlock();
+    return;
+  }
+  if (!same) {
+    dvr_workspace_invalidate(vc.ws);
+    vc.volume = in.volume;
+    vc.version = version;
+    vc.stream = stream;
+  }
+  c.o.workspace = vc.ws;
+}
+
+void drop_volume_caches() {
+  for (VolumeCache& vc : g_cache) {
+    std::lock_guard<std::mutex> lock(vc.m);
+    if (vc.ws) dvr_workspace_destroy(vc.ws);
+    vc.ws = nullptr;
+    vc.volume = torch::Tensor();
+  }
+}
+
 }  // namespace
 
 void Renderer::checkInputs(const RendererInputsHost& inputsHost, int& B, int& W, int& H, int& X, int& Y, int& Z,
@@ -188,15 +258,39 @@ bool Renderer::initCuda() { return c10::cuda::device_count() > 0; }
 void Renderer::setCudaCacheDir(const std::filesystem::path&) {}
 void Renderer::reloadCudaKernels() {}
 void Renderer::disableCudaCache() {}
-void Renderer::cleanupCuda() {}
+void Renderer::cleanupCuda() {  // frees what the library holds on the device: volume caches and scratch pool pages
+  drop_volume_caches();
+  dvr_trim_scratch();
+}
 void Renderer::setCudaSyncMode(bool sync) { raise_on_error(dvr_set_option("sync_mode", sync ? 1 : 0)); }
 bool Renderer::getCudaSyncMode() { return getOption("sync_mode") != 0; }
 void Renderer::setCudaDebugMode(bool) {}
 
-void Renderer::setOption(const std::string& name, int value) { raise_on_error(dvr_set_option(name.c_str(), value)); }
+void Renderer::setOption(const std::string& name, int value) {
+  if (name == "compat_stepsize_overwrite") { g_compat_stepsize = value != 0; return; }
+  if (name == "volume_layout") {
+    TORCH_CHECK(value >= -1 && value <= 1, "volume_layout must be -1, 0 or 1");
+    g_volume_layout = value;
+    return;
+  }
+  if (name == "volume_cache") {
+    g_volume_cache = value != 0;
+    if (!value) drop_volume_caches();
+    return;
+  }
+  raise_on_error(dvr_set_option(name.c_str(), value));
+}
 int Renderer::getOption(const std::string& name) {
+  if (name == "compat_stepsize_overwrite") return g_compat_stepsize.load();
+  if (name == "volume_layout") return g_volume_layout.load();
+  if (name == "volume_cache") return g_volume_cache.load();
   int32_t v = 0;
   raise_on_error(dvr_get_option(name.c_str(), &v));
+  return v;
+}
+long long Renderer::stat(const std::string& name) {
+  int64_t v = 0;
+  raise_on_error(dvr_get_stat(name.c_str(), &v));
   return v;
 }
 long long Renderer::launchCount() { return dvr_launch_count(); }
@@ -206,7 +300,10 @@ void Renderer::renderForward(const RendererInputsHost& inputsHost, RendererOutpu
   const c10::cuda::CUDAGuard guard(dev);
   const DvrInputs in = to_c(inputsHost, dev);
   const DvrOutputs out = to_c(outputsHost, dev, "color");
-  raise_on_error(dvr_render_forward(&in, &out, current_stream(dev)));
+  void* stream = current_stream(dev);
+  CallOptions opt;
+  fill_options(opt, inputsHost, dev, stream);
+  raise_on_error(dvr_render_forward_ex(&in, &out, &opt.o, stream));
 }
 
 void Renderer::renderForwardGradients(const RendererInputsHost& inputsHost,
@@ -219,7 +316,10 @@ void Renderer::renderForwardGradients(const RendererInputsHost& inputsHost,
   const DvrForwardDifferencesSettings st = to_c(differencesSettingsHost, dev);
   const DvrOutputs out = to_c(outputsHost, dev, "color");
   const DvrTensor g = real_view(gradientsOut, "gradientsOut", dev);
-  raise_on_error(dvr_render_forward_gradients(&in, &st, &out, &g, current_stream(dev)));
+  void* stream = current_stream(dev);
+  CallOptions opt;
+  fill_options(opt, inputsHost, dev, stream);
+  raise_on_error(dvr_render_forward_gradients_ex(&in, &st, &out, &g, &opt.o, stream));
 }
 
 void Renderer::forwardVariablesToGradients(const torch::Tensor& forwardVariables,
@@ -251,7 +351,10 @@ void Renderer::renderAdjoint(const RendererInputsHost& inputsHost, const Rendere
   if (!adj_outputs.hasTFDerivatives && !adj_outputs.hasCameraDerivatives && !adj_outputs.hasStepSizeDerivatives &&
       !adj_outputs.hasVolumeDerivatives)
     throw std::runtime_error("At least one adjoint variable must be activated!");  // renderer.cpp:711-716
-  raise_on_error(dvr_render_adjoint(&in, &fwd, &ac, &adj, current_stream(dev)));
+  void* stream = current_stream(dev);
+  CallOptions opt;
+  fill_options(opt, inputsHost, dev, stream);
+  raise_on_error(dvr_render_adjoint_ex(&in, &fwd, &ac, &adj, &opt.o, stream));
 }
 
 void Renderer::compareToImage(const torch::Tensor& colorInput, const torch::Tensor& gradientsInput,

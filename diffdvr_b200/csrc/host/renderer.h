@@ -123,7 +123,7 @@ class Renderer {
   static void setCudaCacheDir(const std::filesystem::path& path);  // no-op: nothing is compiled at run time
   static void reloadCudaKernels();                                  // no-op
   static void disableCudaCache();                                   // no-op
-  static void cleanupCuda();                                        // no-op
+  static void cleanupCuda();  // frees the volume caches and the library's scratch pool (nothing else to clean up)
   static void setCudaSyncMode(bool sync);
   static bool getCudaSyncMode();
   static void setCudaDebugMode(bool debug);                         // no-op (kernels carry -lineinfo)
@@ -146,10 +146,15 @@ class Renderer {
                              const torch::Tensor& colorReference, torch::Tensor& differenceOut,
                              torch::Tensor& gradientsOut, bool reduce = false);
 
-  // extensions (not in the reference): library options of include/dvr_b200.h
+  // extensions (not in the reference). Options of this static facade, passed to the C-ABI per call (DvrCallOptions):
+  //   "compat_stepsize_overwrite" 0/1, "volume_layout" -1/0/1 (include/dvr_b200.h),
+  //   "volume_cache" 1 (default): one QUAD copy per device cached on the volume tensor and torch's version counter, so
+  //   forward, forward-mode and adjoint calls on an unchanged volume share it; 0 disables and frees the cache.
+  // "sync_mode" is the library's own process-wide switch.
   static void setOption(const std::string& name, int value);
   static int getOption(const std::string& name);
   static long long launchCount();
+  static long long stat(const std::string& name);  // dvr_get_stat: "quad_builds", "quad_reuses", ...
 };
 
 }  // namespace renderer

@@ -20,7 +20,9 @@
  *    (renderer/renderer_settings.cuh:81-146);
  *  - adjoint outputs are ACCUMULATED into caller-zeroed tensors
  *    (renderer/renderer_settings.cuh:227-229);
- *  - no device allocations except the stream-ordered scratch of "volume_layout" (below);
+ *  - no device allocations except the QUAD scratch described at DvrCallOptions / DvrWorkspace (below);
+ *  - reentrant: no process-wide state changes the result of a call (options travel per call in
+ *    DvrCallOptions; the only global switch is "sync_mode", which the reference has too);
  *  - every function returns DVR_OK (0) or a negative error code, never throws;
  *    dvr_last_error() returns a thread-local message for the last failure;
  *  - launches are asynchronous on `stream` (a cudaStream_t passed as void*), like the
@@ -256,32 +258,90 @@ DVR_API int dvr_count_cell_visits(const DvrInputs* inputs, const DvrTensor* term
  * Any out pointer may be NULL. */
 DVR_API int dvr_check_inputs(const DvrInputs* inputs, int32_t* B, int32_t* X, int32_t* Y, int32_t* Z);
 
-/* 1 if the (filter, camera, tf, blend) combination has a precompiled instance, else 0.
- * Replaces "does it compile under NVRTC" (unittests/testCudaCompilation.cpp:109-287). */
+/* ---- per-call options and the volume-layout workspace (ABI version 2) ------------------------------
+ *
+ * Trilinear sampling has two layouts:
+ *   in place : the caller's strided tensor, 8 x 4-byte loads and 8 scalar REDs per cell;
+ *   QUAD     : a 16-byte-per-voxel copy holding the (y,z) 2x2 footprint of every voxel: 2 x 16-byte loads per
+ *              cell; the adjoint accumulates into a scratch of the same layout with 2 x red.v4 per cell, which
+ *              is folded into adj_volume afterwards.
+ * Where the QUAD buffers live:
+ *   - options == NULL or options->workspace == NULL: stream-ordered scratch per call from a PRIVATE memory pool of
+ *     the library (cudaMallocFromPoolAsync on `stream`; the device's default pool is not touched). The copy is
+ *     rebuilt, the gradient scratch zeroed and folded on every call. dvr_trim_scratch() returns the pool's pages.
+ *   - options->workspace != NULL: the buffers belong to the workspace and persist. The copy is rebuilt only when
+ *     the volume tensor's (ptr, sizes, strides) differ from the cached key or after dvr_workspace_set_volume /
+ *     dvr_workspace_invalidate (the caller's "version": call one of them when the CONTENTS changed).
+ *     Between dvr_workspace_begin_volume_gradient and dvr_workspace_end_volume_gradient every adjoint call
+ *     accumulates into ONE zeroed gradient scratch that is folded into adj_volume once at the end (the fold is
+ *     linear), instead of memset + fold per call.
+ * A workspace must be used from one stream at a time (its buffers are not stream-ordered). */
+typedef struct DvrWorkspace DvrWorkspace;
+
+typedef struct DvrCallOptions {
+  uint32_t struct_size;              /* sizeof(DvrCallOptions), set by dvr_call_options_init */
+  int32_t volume_layout;             /* -1 automatic (QUAD when rays * 64 >= voxels, or a valid workspace copy
+                                        exists), 0 in place, 1 QUAD */
+  int32_t compat_stepsize_overwrite; /* adjoint: 1 reproduces the reference's stepsize recurrence bit for bit (the
+                                        blend term of the stepsize adjoint is OVERWRITTEN every sample,
+                                        renderer/renderer_kernels.cuh:393-395 with renderer_blending.cuh:93,158);
+                                        0 (default) accumulates it (the mathematically complete gradient) */
+  int32_t sync;                      /* 1: cudaStreamSynchronize after the launches of this call */
+  int64_t max_scratch_bytes;         /* cap on the per-call / workspace QUAD buffers of this call; above it the call
+                                        takes the in-place path (counted, see dvr_get_stat). <= 0: 16 GiB */
+  DvrWorkspace* workspace;           /* may be NULL */
+} DvrCallOptions;
+
+DVR_API void dvr_call_options_init(DvrCallOptions* options); /* the defaults: -1, 0, 0, 0, NULL */
+
+DVR_API DvrWorkspace* dvr_workspace_create(void);            /* on the current device; NULL on failure */
+DVR_API void dvr_workspace_destroy(DvrWorkspace* ws);        /* frees its device buffers (synchronises) */
+/* Builds the QUAD copy of `volume` ((B)*X*Y*Z) now and caches it under the tensor's (ptr, sizes, strides). */
+DVR_API int dvr_workspace_set_volume(DvrWorkspace* ws, const DvrTensor* volume, void* stream);
+/* Marks the cached copy stale (the next call that wants it rebuilds it). */
+DVR_API int dvr_workspace_invalidate(DvrWorkspace* ws);
+/* Zeroes the workspace's QUAD gradient scratch for adj_volume ((B)*X*Y*Z) and opens an accumulation scope. */
+DVR_API int dvr_workspace_begin_volume_gradient(DvrWorkspace* ws, const DvrTensor* adj_volume, void* stream);
+/* Folds the scratch into adj_volume (accumulating) and closes the scope. */
+DVR_API int dvr_workspace_end_volume_gradient(DvrWorkspace* ws, const DvrTensor* adj_volume, void* stream);
+DVR_API int64_t dvr_workspace_bytes(const DvrWorkspace* ws); /* device bytes currently owned */
+
+/* The render entry points with per-call options (options == NULL: the defaults). The plain entry points above
+ * are these with options == NULL. */
+DVR_API int dvr_render_forward_ex(const DvrInputs* inputs, const DvrOutputs* outputs, const DvrCallOptions* options,
+                                  void* stream);
+DVR_API int dvr_render_forward_gradients_ex(const DvrInputs* inputs, const DvrForwardDifferencesSettings* settings,
+                                            const DvrOutputs* outputs, const DvrTensor* gradients_out,
+                                            const DvrCallOptions* options, void* stream);
+DVR_API int dvr_render_adjoint_ex(const DvrInputs* inputs, const DvrOutputs* outputs_from_forward,
+                                  const DvrTensor* adj_color, const DvrAdjointOutputs* adj_outputs,
+                                  const DvrCallOptions* options, void* stream);
+
+/* Releases the pages the library's private scratch pool holds on the current device. */
+DVR_API int dvr_trim_scratch(void);
+
+/* Which precompiled instances exist. Replaces "does it compile under NVRTC"
+ * (unittests/testCudaCompilation.cpp:109-287). Generated from the same list that declares and dispatches the
+ * per-(tf, blend) instance translation units (DVR_FOR_EACH_*_INSTANCE in csrc/dvr_launch.h), so it cannot drift
+ * from what links. pass: one of DvrPass. */
+enum DvrPass { DVR_PASS_FORWARD = 0, DVR_PASS_FORWARD_GRADIENTS = 1, DVR_PASS_ADJOINT = 2 };
+DVR_API int dvr_has_variant_pass(int32_t pass, int32_t volume_filter_mode, int32_t camera_mode, int32_t tf_mode,
+                                 int32_t blend_mode);
+/* forward AND adjoint available (the pair every optimisation needs) */
 DVR_API int dvr_has_variant(int32_t volume_filter_mode, int32_t camera_mode, int32_t tf_mode,
                     int32_t blend_mode);
 
-/* Runtime options (replace Renderer::setCudaSyncMode etc., renderer/renderer.h:128-150,
- * and the compile-time switches of the reference):
- *   "sync_mode"                 0/1  cudaStreamSynchronize after every launch (default 0)
- *   "compat_stepsize_overwrite" 0/1  1 reproduces the reference's adjoint stepsize
- *                                    recurrence bit-for-bit (the blend term of the stepsize
- *                                    adjoint is overwritten every sample,
- *                                    renderer/renderer_kernels.cuh:393-395 with
- *                                    renderer/renderer_blending.cuh:93,158); 0 (default)
- *                                    accumulates it (mathematically complete gradient).
- *   "volume_layout"             trilinear forward / adjoint:
- *                               0 = sample the caller's strided tensor in place (8 x 4-byte loads
- *                                   and 8 scalar REDs per cell),
- *                               1 = build a QUAD copy of the volume per call (16 bytes per voxel
- *                                   holding the (y,z) 2x2 footprint: 2 x 16-byte loads per cell) and,
- *                                   in the adjoint, accumulate into a QUAD scratch with 2 x red.v4
- *                                   per cell that is folded into adj_volume afterwards; scratch is
- *                                   stream-ordered (cudaMallocAsync on `stream`),
- *                               -1 (default) = automatic: 1 when rays * 64 >= voxels
+/* Process-wide switch, like Renderer::setCudaSyncMode (renderer/renderer.h:128-150):
+ *   "sync_mode" 0/1  cudaStreamSynchronize after every launch (default 0)
+ * Everything that changes RESULTS or memory use is per call (DvrCallOptions).
  * Returns DVR_OK or DVR_ERR_INVALID_ARGUMENT for an unknown name. */
 DVR_API int dvr_set_option(const char* name, int32_t value);
 DVR_API int dvr_get_option(const char* name, int32_t* value);
+
+/* Counters since load: "launches", "quad_builds" (QUAD copies built), "quad_reuses" (calls served by a cached
+ * workspace copy), "quad_fallbacks" (calls that wanted the QUAD layout and took the in-place path: scratch above
+ * the cap, allocation failure, aliased adj_volume strides), "folds". */
+DVR_API int dvr_get_stat(const char* name, int64_t* value);
 
 /* Number of kernel launches issued by this library since load (for bench accounting). */
 DVR_API int64_t dvr_launch_count(void);
@@ -302,7 +362,7 @@ DVR_API const char* dvr_last_error(void);
 
 /* ABI version of this header. */
 DVR_API int32_t dvr_abi_version(void);
-#define DVR_ABI_VERSION 1
+#define DVR_ABI_VERSION 2
 
 #ifdef __cplusplus
 }

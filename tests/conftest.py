@@ -13,6 +13,14 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
 
 
+@pytest.fixture(autouse=True)
+def _parity_log_test_id(request):
+    """Names the running test in the parity log (tests/parity_log.py)."""
+    import parity_log
+    parity_log.set_current_test(request.node.nodeid)
+    yield
+
+
 def pytest_collection_modifyitems(config, items):
     try:
         import torch

@@ -59,13 +59,14 @@ def fg_settings(sc, fg):
     return dict(fg)
 
 
-def run(lib, sc, flags, fg, runner=None, forward_from=None):
+def run(lib, sc, flags, fg, runner=None, forward_from=None, runner_kwargs=None):
     """Runs forward, adjoint and, if ``fg``, forward-mode on ``sc`` through ``lib`` (host pointers) or
     through ``runner`` (the GPU runner module, device pointers). Returns a dict of numpy arrays."""
+    rk = runner_kwargs or {}
     if runner is None:
         color, term = scenes.np_forward(lib, sc)
     else:
-        color, term = runner.forward(sc)
+        color, term = runner.forward(sc, **rk)
     out = {"color": color, "term": term}
     adj_color = np.random.RandomState(ADJ_SEED).randn(*color.shape).astype(np.float32)
     # the adjoint consumes the GOLDEN forward outputs when given, so that a +-1 terminationIndex
@@ -74,7 +75,7 @@ def run(lib, sc, flags, fg, runner=None, forward_from=None):
     if runner is None:
         adj = scenes.np_adjoint(lib, sc, c_in, t_in, adj_color, **flags)
     else:
-        adj = runner.adjoint(sc, c_in, t_in, adj_color, **flags)
+        adj = runner.adjoint(sc, c_in, t_in, adj_color, **flags, **rk)
     out.update(adj)
     st = fg_settings(sc, fg)
     if st is not None:
@@ -89,6 +90,6 @@ def run(lib, sc, flags, fg, runner=None, forward_from=None):
             g = np.zeros((B, H, W, D, 4), np.float32)
             lib.render_forward_gradients(inp, s, c2, t2, g)
         else:
-            c2, t2, g = runner.forward_gradients(sc, D, **st)
+            c2, t2, g = runner.forward_gradients(sc, D, **st, **rk)
         out["fg_color"], out["fg_term"], out["fg_gradients"] = c2, t2, g
     return out

@@ -16,19 +16,19 @@ def to_cuda(a: np.ndarray):
     return t
 
 
-def forward(scene, lib=None):
+def forward(scene, lib=None, options=None):
     lib = lib or capi.load()
     B, H, W = scene.B, scene.H, scene.W
     inp = scene.inputs(to_cuda)
     color = torch.empty(B, H, W, 4, device="cuda")
     term = torch.empty(B, H, W, dtype=torch.int32, device="cuda")
-    lib.render_forward(inp, color, term, torch.cuda.current_stream().cuda_stream)
+    lib.render_forward(inp, color, term, torch.cuda.current_stream().cuda_stream, options)
     torch.cuda.synchronize()
     return color.cpu().numpy(), term.cpu().numpy()
 
 
 def adjoint(scene, color, term, adj_color, *, volume=False, step=False, camera=False, tf=False,
-            step_shape=None, delayed=False, lib=None):
+            step_shape=None, delayed=False, lib=None, options=None):
     lib = lib or capi.load()
     B, H, W = scene.B, scene.H, scene.W
     inp = scene.inputs(to_cuda)
@@ -44,13 +44,13 @@ def adjoint(scene, color, term, adj_color, *, volume=False, step=False, camera=F
         out["adj_tf"] = torch.zeros(scene.tf.shape, device="cuda")
     adj = capi.make_adjoint_outputs(tf_delayed_accumulation=delayed, **out)
     c, t, a = torch.from_numpy(color).cuda(), torch.from_numpy(term).cuda(), torch.from_numpy(adj_color).cuda()
-    lib.render_adjoint(inp, c, t, a, adj, torch.cuda.current_stream().cuda_stream)
+    lib.render_adjoint(inp, c, t, a, adj, torch.cuda.current_stream().cuda_stream, options)
     torch.cuda.synchronize()
     return {k: v.cpu().numpy() for k, v in out.items()}
 
 
 def forward_gradients(scene, D, *, d_stepsize=-1, d_ray_start=(-1, -1, -1), d_ray_dir=(-1, -1, -1), d_tf=None,
-                      lib=None):
+                      lib=None, options=None):
     lib = lib or capi.load()
     B, H, W = scene.B, scene.H, scene.W
     inp = scene.inputs(to_cuda)
@@ -59,7 +59,7 @@ def forward_gradients(scene, D, *, d_stepsize=-1, d_ray_start=(-1, -1, -1), d_ra
     color = torch.empty(B, H, W, 4, device="cuda")
     term = torch.empty(B, H, W, dtype=torch.int32, device="cuda")
     grad = torch.zeros(B, H, W, D, 4, device="cuda")
-    lib.render_forward_gradients(inp, st, color, term, grad, torch.cuda.current_stream().cuda_stream)
+    lib.render_forward_gradients(inp, st, color, term, grad, torch.cuda.current_stream().cuda_stream, options)
     torch.cuda.synchronize()
     return color.cpu().numpy(), term.cpu().numpy(), grad.cpu().numpy()
 

@@ -80,7 +80,10 @@ def ref(real_bits: int = 32):
     if key not in _cache:
         path = os.path.join(ORACLE_DIR, "_ref", f"libdvr_ref{real_bits}.so")
         if not os.path.exists(path) and os.path.isdir("/root/reference/renderer"):
-            _make(f"_ref/libdvr_ref{real_bits}.so")
+            # the reference is here: a missing build is an error, not a reason to fall back to the port silently
+            if not _make(f"_ref/libdvr_ref{real_bits}.so"):
+                raise RuntimeError(f"/root/reference is present but oracle/_ref/libdvr_ref{real_bits}.so does not build "
+                                   "(run `make -C oracle ref` to see why)")
         _cache[key] = OracleLibrary(path, f"dvrref{real_bits}_", real_bits) if os.path.exists(path) else None
     return _cache[key]
 

@@ -225,12 +225,19 @@ def per_ray_errors(got, want):
 FACE_EPS = 3e-5  # voxels; ~8x the fp32 round-off of a sample coordinate on a <=64^3 test volume
 
 
-def face_sensitive_rays(scene: Scene, term, eps=FACE_EPS):
+def face_eps(n: int) -> float:
+    """8x the fp32 round-off of a sample coordinate in an n^3 volume (n * 2^-24 voxels), never below FACE_EPS."""
+    return max(FACE_EPS, 8.0 * n * 2.0 ** -24)
+
+
+def face_sensitive_rays(scene: Scene, term, eps=None):
     """Boolean (B,H,W) mask of rays with a sample within ``eps`` voxels of a trilinear cell face
     (computed in fp64 by the oracle's diagnostic, oracle/dvr_oracle.cpp face_distance)."""
     import oracle_loader as ol
     if scene.filter_mode != capi.FILTER_TRILINEAR:
         return np.zeros(term.shape, dtype=bool)
+    if eps is None:
+        eps = face_eps(max(scene.volume.shape[1:]))
     fd = np.ones(term.shape, dtype=np.float64)
     inp = scene.inputs(lambda a: a.astype(np.float64) if a.dtype != np.int32 else a)
     ol.port(64).face_distance(inp, np.ascontiguousarray(term, dtype=np.int32), fd)
@@ -247,9 +254,21 @@ def assert_position_gradient_close(name, got, want32, want64, tol=1e-4, sensitiv
         oracle, or no further from it than 1.5x the fp32 oracle is;
       * on the face-sensitive rays: median per-ray error no worse than 2x the fp32 oracle's and
         every ray within the size of one flipped sample (half the RMS ray gradient)."""
-    if rel_l2(got, want32) <= tol:
+    import parity_log
+    e32 = rel_l2(got, want32)
+    if e32 <= tol:
+        parity_log.record(name, "strict", rel_l2=e32, tol=tol)
         return
-    assert sensitive is not None, f"{name}: rel-L2 {rel_l2(got, want32):.2e} > {tol} and no face mask given"
+    if callable(want64):  # computed only when the strict gate fails (expensive at the config sizes)
+        want64 = want64()
+    if callable(sensitive):
+        sensitive = sensitive()
+    assert sensitive is not None, f"{name}: rel-L2 {e32:.2e} > {tol} and no face mask given"
+    parity_log.record(name, "relaxed:face-sensitive-rays", rel_l2=e32, tol=tol,
+                      rel_l2_vs_fp64=rel_l2(got, want64), fp32_oracle_noise=rel_l2(want32, want64),
+                      masked_fraction=float(np.mean(sensitive)),
+                      rel_l2_unmasked_vs_fp64=rel_l2(np.asarray(got)[~sensitive], np.asarray(want64)[~sensitive])
+                      if (~sensitive).any() else 0.0)
     lead = sensitive.shape
     g = np.asarray(got, dtype=np.float64).reshape(lead + (-1,))
     w32 = np.asarray(want32, dtype=np.float64).reshape(lead + (-1,))

@@ -34,7 +34,7 @@ def test_library_loads_without_gpu_and_exports_every_declared_symbol():
     lib = capi.load()   # raises if the .so is missing: there is no fallback
     for s in declared_symbols():
         assert hasattr(lib.lib, s), f"{s} declared in include/dvr_b200.h but not exported"
-    assert lib.lib.dvr_abi_version() == 1
+    assert lib.lib.dvr_abi_version() == 2
     # nothing else with default visibility leaks out of the library
     out = subprocess.run(["nm", "-D", "--defined-only", capi.library_path()], capture_output=True, text=True).stdout
     exported = {l.split()[-1] for l in out.splitlines() if " T " in l}
@@ -45,8 +45,9 @@ def test_struct_layout_matches_the_c_header(tmp_path):
     src = tmp_path / "layout.c"
     src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "dvr_b200.h"\n'
                    "int main(void){\n"
-                   'printf("%zu %zu %zu %zu %zu\\n", sizeof(DvrTensor), sizeof(DvrInputs), sizeof(DvrOutputs),'
-                   " sizeof(DvrForwardDifferencesSettings), sizeof(DvrAdjointOutputs));\n"
+                   'printf("%zu %zu %zu %zu %zu %zu %zu\\n", sizeof(DvrTensor), sizeof(DvrInputs), sizeof(DvrOutputs),'
+                   " sizeof(DvrForwardDifferencesSettings), sizeof(DvrAdjointOutputs), sizeof(DvrCallOptions),"
+                   " offsetof(DvrCallOptions, workspace));\n"
                    'printf("%zu %zu %zu %zu %zu\\n", offsetof(DvrInputs, tf), offsetof(DvrInputs, step_size_value),'
                    " offsetof(DvrInputs, blending_early_out), offsetof(DvrAdjointOutputs, adj_tf),"
                    " offsetof(DvrForwardDifferencesSettings, d_tf));\nreturn 0;}\n")
@@ -54,7 +55,15 @@ def test_struct_layout_matches_the_c_header(tmp_path):
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
     a, b = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines()
     assert [int(v) for v in a.split()] == [ctypes.sizeof(c) for c in (
-        capi.DvrTensor, capi.DvrInputs, capi.DvrOutputs, capi.DvrForwardDifferencesSettings, capi.DvrAdjointOutputs)]
+        capi.DvrTensor, capi.DvrInputs, capi.DvrOutputs, capi.DvrForwardDifferencesSettings, capi.DvrAdjointOutputs,
+        capi.DvrCallOptions)] + [capi.DvrCallOptions.workspace.offset]
+    # dvr_call_options_init writes the documented defaults, and the ctypes helper builds the same struct
+    o = capi.DvrCallOptions()
+    capi.load().lib.dvr_call_options_init(ctypes.byref(o))
+    d = capi.make_call_options()
+    assert (o.struct_size, o.volume_layout, o.compat_stepsize_overwrite, o.sync, o.max_scratch_bytes, o.workspace) == \
+           (d.struct_size, d.volume_layout, d.compat_stepsize_overwrite, d.sync, d.max_scratch_bytes, d.workspace) == \
+           (ctypes.sizeof(capi.DvrCallOptions), -1, 0, 0, 0, None)
     assert [int(v) for v in b.split()] == [
         capi.DvrInputs.tf.offset, capi.DvrInputs.step_size_value.offset, capi.DvrInputs.blending_early_out.offset,
         capi.DvrAdjointOutputs.adj_tf.offset, capi.DvrForwardDifferencesSettings.d_tf.offset]
@@ -79,13 +88,17 @@ def test_has_variant_covers_the_reference_instantiation_set():
 
 def test_options_round_trip_and_unknown_option():
     lib = capi.load()
-    for name in ("sync_mode", "compat_stepsize_overwrite"):
+    for name in ("sync_mode",):
         old = lib.get_option(name)
         lib.set_option(name, 1)
         assert lib.get_option(name) == 1
         lib.set_option(name, old)
     with pytest.raises(capi.DvrError):
         lib.set_option("no_such_option", 1)
+    # options that change results are per call (DvrCallOptions), never process state
+    for name in ("compat_stepsize_overwrite", "volume_layout"):
+        with pytest.raises(capi.DvrError, match="per call"):
+            lib.set_option(name, 1)
 
 
 def test_check_inputs_shapes_and_reference_error_messages():

@@ -37,17 +37,17 @@ def world():
                            camera_fov_y_radians=math.radians(45.0), step_size=step, tf_mode=tf_mode, tf=tf,
                            blend_mode=capi.BLEND_BEER_LAMBERT)
 
-    def forward(inp, B=VIEWS):
+    def forward(inp, B=VIEWS, options=None):
         color = torch.empty(B, RES, RES, 4, device=dev)
         term = torch.empty(B, RES, RES, dtype=torch.int32, device=dev)
-        lib.render_forward(inp, color, term)
+        lib.render_forward(inp, color, term, options=options)
         torch.cuda.synchronize()
         return color, term
 
-    def adjoint(inp, color, term, adj_color, **extra):
+    def adjoint(inp, color, term, adj_color, options=None, **extra):
         adj_volume = torch.zeros(1, N, N, N, device=dev)
         adj = capi.make_adjoint_outputs(adj_volume=adj_volume, **extra)
-        lib.render_adjoint(inp, color, term, adj_color, adj)
+        lib.render_adjoint(inp, color, term, adj_color, adj, options=options)
         torch.cuda.synchronize()
         return adj_volume
 
@@ -75,14 +75,11 @@ def test_layouts_agree_at_full_size(world):
     inp = world["inputs"](world["volume"])
     g = torch.Generator(device="cuda").manual_seed(5)
     out = {}
-    try:
-        for layout in (0, 1):
-            lib.set_option("volume_layout", layout)
-            color, term = world["forward"](inp)
-            adj_color = torch.randn(color.shape, device="cuda", generator=g) if layout == 0 else adj_color
-            out[layout] = (color, term, world["adjoint"](inp, color, term, adj_color))
-    finally:
-        lib.set_option("volume_layout", -1)
+    for layout in (0, 1):
+        opts = capi.make_call_options(volume_layout=layout)
+        color, term = world["forward"](inp, options=opts)
+        adj_color = torch.randn(color.shape, device="cuda", generator=g) if layout == 0 else adj_color
+        out[layout] = (color, term, world["adjoint"](inp, color, term, adj_color, options=opts))
     assert torch.equal(out[0][0], out[1][0]) and torch.equal(out[0][1], out[1][1])
     assert rel(out[1][2], out[0][2]) <= 2e-6
 

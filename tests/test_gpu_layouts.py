@@ -20,17 +20,12 @@ CASES = {name: (sc, flags, fg) for name, sc, flags, fg in golden_cases.cases()
 
 def _run(layout, sc, flags, gold):
     lib = capi.load()
-    lib.set_option("volume_layout", layout)
-    lib.set_option("compat_stepsize_overwrite", 1)
-    try:
-        n0 = lib.launch_count()
-        color, term = gr.forward(sc, lib)
-        launches = lib.launch_count() - n0
-        adj_color = np.random.RandomState(golden_cases.ADJ_SEED).randn(*color.shape).astype(np.float32)
-        adj = gr.adjoint(sc, gold["color"], gold["term"], adj_color, lib=lib, **flags)
-    finally:
-        lib.set_option("volume_layout", -1)
-        lib.set_option("compat_stepsize_overwrite", 0)
+    opts = capi.make_call_options(volume_layout=layout, compat_stepsize_overwrite=True)
+    n0 = lib.launch_count()
+    color, term = gr.forward(sc, lib, options=opts)
+    launches = lib.launch_count() - n0
+    adj_color = np.random.RandomState(golden_cases.ADJ_SEED).randn(*color.shape).astype(np.float32)
+    adj = gr.adjoint(sc, gold["color"], gold["term"], adj_color, lib=lib, options=opts, **flags)
     return color, term, adj, launches
 
 
@@ -52,7 +47,6 @@ def test_quad_copy_equals_in_place_sampling(name):
 
 def test_automatic_choice_follows_the_work_estimate():
     lib = capi.load()
-    assert lib.get_option("volume_layout") == -1
     big = scenes.make_scene(n=48, W=4, H=4, B=1, seed=1)      # 16 rays, 110592 voxels: in place
     small = scenes.make_scene(n=16, W=32, H=32, B=1, seed=1)  # 1024 rays, 4096 voxels: copy
     for sc, want in ((big, 1), (small, 2)):
@@ -72,13 +66,9 @@ def test_forward_mode_quad_copy_equals_in_place_sampling(name):
     lib = capi.load()
     res = {}
     for layout in (0, 1):
-        lib.set_option("volume_layout", layout)
-        try:
-            n0 = lib.launch_count()
-            res[layout] = gr.forward_gradients(sc, lib=lib, **st)
-            launches = lib.launch_count() - n0
-        finally:
-            lib.set_option("volume_layout", -1)
+        n0 = lib.launch_count()
+        res[layout] = gr.forward_gradients(sc, lib=lib, options=capi.make_call_options(volume_layout=layout), **st)
+        launches = lib.launch_count() - n0
         passes = -(-st["D"] // 8) if st["D"] > 6 else 1
         assert launches == passes + layout  # ONE copy serves every pass
     (c0, t0, g0), (c1, t1, g1) = res[0], res[1]

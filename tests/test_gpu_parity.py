@@ -29,11 +29,19 @@ def oracles():
 
 
 def check_grad(name, got, want32, want64):
+    """adj_volume / adj_tf (no position derivative inside): the STRICT 1e-4 gate against the fp32 oracle, nothing
+    else. Per-ray quantities that reach this function (broadcast adj_stepSize) may also pass against the fp64 oracle
+    relative to the fp32 oracle's own noise; which branch was taken is recorded (tests/parity_log.py)."""
+    import parity_log
     e32 = scenes.rel_l2(got, want32)
     if e32 <= GRAD_TOL:
+        parity_log.record(name, "strict", rel_l2=e32, tol=GRAD_TOL)
         return
+    assert name not in ("adj_volume", "adj_tf"), f"{name}: rel-L2 vs fp32 oracle {e32:.2e} > {GRAD_TOL}"
     noise = scenes.rel_l2(want32, want64)
     e64 = scenes.rel_l2(got, want64)
+    parity_log.record(name, "relaxed:fp64-oracle", rel_l2=e32, tol=GRAD_TOL, rel_l2_vs_fp64=e64,
+                      fp32_oracle_noise=noise)
     assert e64 <= 1.5 * noise + GRAD_TOL, (
         f"{name}: rel-L2 vs fp32 oracle {e32:.2e}, vs fp64 oracle {e64:.2e}, fp32-oracle noise {noise:.2e}")
 
@@ -42,9 +50,12 @@ def run_case(oracles, sc, *, volume=True, step=True, camera=True, tf=True, delay
     o32, o64 = oracles
     want_c, want_t = scenes.np_forward(o32, sc)
     got_c, got_t = gr.forward(sc)
-    assert scenes.rel_l2(got_c, want_c) <= IMG_TOL
+    import parity_log
+    e_img = scenes.rel_l2(got_c, want_c)
+    assert e_img <= IMG_TOL
     # exact for rays that leave through the far side; early-out rays may flip by one sample
     mism = got_t != want_t
+    parity_log.record("image", "strict", rel_l2=e_img, tol=IMG_TOL, term_mismatch=float(mism.mean()))
     assert mism.mean() <= 1e-3
     assert np.all(np.abs(got_t.astype(np.int64) - want_t)[mism] <= 1)
     adj_color = np.random.RandomState(7).randn(*want_c.shape).astype(np.float32)
@@ -133,9 +144,9 @@ def test_stepsize_compat_switch_reproduces_reference_overwrite(oracles):
     c, t = scenes.np_forward(o32, sc)
     adj_color = np.random.RandomState(2).randn(*c.shape).astype(np.float32)
     try:
-        lib.set_option("compat_stepsize_overwrite", 1)
         ol.port_set_option("compat_stepsize_overwrite", 1)
-        got = gr.adjoint(sc, c, t, adj_color, step=True)
+        got = gr.adjoint(sc, c, t, adj_color, step=True,
+                         options=capi.make_call_options(compat_stepsize_overwrite=True))
         want = scenes.np_adjoint(o32, sc, c, t, adj_color, step=True)
         ref = ol.ref(32)
         if ref is not None:  # the reference's own compiled host kernel
@@ -143,7 +154,6 @@ def test_stepsize_compat_switch_reproduces_reference_overwrite(oracles):
             assert scenes.rel_l2(want["adj_step_size"], want_ref["adj_step_size"]) <= 1e-6
         assert scenes.rel_l2(got["adj_step_size"], want["adj_step_size"]) <= GRAD_TOL
     finally:
-        lib.set_option("compat_stepsize_overwrite", 0)
         ol.port_set_option("compat_stepsize_overwrite", 0)
 
 

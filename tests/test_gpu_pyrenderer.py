@@ -27,7 +27,8 @@ def test_pyrenderer_matches_golden_reference_outputs(name):
     pyr.set_option("compat_stepsize_overwrite", 1)
     try:
         out = golden_cases.run(None, sc, flags, fg, runner=pr, forward_from=(gold["color"], gold["term"]))
-        via_ctypes = golden_cases.run(None, sc, flags, fg, runner=gr, forward_from=(gold["color"], gold["term"]))
+        via_ctypes = golden_cases.run(None, sc, flags, fg, runner=gr, forward_from=(gold["color"], gold["term"]),
+                                      runner_kwargs=dict(options=capi.make_call_options(compat_stepsize_overwrite=True)))
     finally:
         pyr.set_option("compat_stepsize_overwrite", 0)
     assert pyr.launch_count() > n0                      # the CUDA library did the work

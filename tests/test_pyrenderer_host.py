@@ -102,10 +102,17 @@ def test_cpu_tensors_are_rejected_there_is_no_cpu_backend():
 
 
 def test_options_and_control_shims():
-    assert pyr.get_option("compat_stepsize_overwrite") == 0
+    # options of the static facade (passed to the C-ABI per call) ...
+    assert pyr.get_option("compat_stepsize_overwrite") == 0 and pyr.get_option("volume_layout") == -1
+    assert pyr.get_option("volume_cache") == 1
     pyr.set_option("compat_stepsize_overwrite", 1)
-    assert capi.load().get_option("compat_stepsize_overwrite") == 1   # one library behind both front ends
+    assert pyr.get_option("compat_stepsize_overwrite") == 1
     pyr.set_option("compat_stepsize_overwrite", 0)
+    # ... and the library's one process-wide switch: one library behind both front ends
+    pyr.set_option("sync_mode", 1)
+    assert capi.load().get_option("sync_mode") == 1
+    pyr.set_option("sync_mode", 0)
+    assert pyr.stat("launches") == pyr.launch_count()
     with pytest.raises(RuntimeError):
         pyr.set_option("no_such_option", 1)
     pyr.set_cuda_sync_mode(True)
