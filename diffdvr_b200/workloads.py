@@ -88,6 +88,18 @@ class Workload:
                               camera_ray_dir=conv(rd), **kw)
         return inp
 
+    def inputs_from(self, volume, tf, cams, res: Optional[int] = None) -> capi.Inputs:
+        """capi.Inputs over tensors the caller already holds: ``cams`` = (viewports,) for the ReferenceFrame camera or
+        (ray_start, ray_dir) for per-pixel rays. No host work (the per-call path of bench.py)."""
+        res = res or self.res
+        box_min, box_size = synthetic.default_box(self.n)
+        kw = dict(screen_size=(res, res), volume=volume, box_min=box_min, box_size=box_size, step_size=self.step_size,
+                  tf_mode=self.tf_mode, tf=tf, blend_mode=capi.BLEND_BEER_LAMBERT)
+        if self.camera == "frame":
+            return capi.Inputs(camera_mode=capi.CAMERA_REFERENCE_FRAME, camera_matrix=cams[0],
+                               camera_fov_y_radians=FOV_Y, **kw)
+        return capi.Inputs(camera_mode=capi.CAMERA_RAY_START_DIR, camera_ray_start=cams[0], camera_ray_dir=cams[1], **kw)
+
     def summary(self) -> dict:
         return {"workload": f"{self.name}: {self.description}", "views": self.views, "image": [self.res, self.res],
                 "volume": [self.n] * 3, "views_per_launch": self.batch, "tf": self.tf_kind,

@@ -46,9 +46,16 @@ def worker(rank, world, port, out_dir):
     try:
         views = multigpu.shard_views(N_VIEWS, rank, world)
         adj_volume, adj_tf = (torch.from_numpy(a) for a in local_gradients(views))
+        # host-sharded parameter: every rank contributes its slice of the volume, all ranks end with all of it
+        full = torch.from_numpy(view_scene(0).volume.copy())
+        b, e = multigpu.shard_bounds(full.numel(), rank, world)
+        gathered = torch.full_like(full, float("nan"))
+        multigpu.allgather_parameter(gathered, full.view(-1)[b:e].clone())
+        # ... and reads back only its slice of the summed gradient
+        mine = multigpu.reduce_scatter_gradient(adj_volume.clone()).clone()
         multigpu.allreduce_gradients([adj_volume, None, adj_tf])
         np.savez(os.path.join(out_dir, f"rank{rank}.npz"), adj_volume=adj_volume.numpy(), adj_tf=adj_tf.numpy(),
-                 views=np.array(views))
+                 views=np.array(views), gathered=gathered.numpy(), grad_slice=mine.numpy(), bounds=np.array([b, e]))
     finally:
         dist.destroy_process_group()
 
@@ -88,4 +95,20 @@ def test_two_ranks_sum_to_the_single_process_gradient(tmp_path):
         # every rank holds the full sum; fp32 summation order differs -> gradient tolerance
         assert scenes.rel_l2(got["adj_volume"], want_volume) <= 1e-6
         assert scenes.rel_l2(got["adj_tf"], want_tf) <= 1e-6
+        assert np.array_equal(got["gathered"], view_scene(0).volume)
+        b, e = got["bounds"]
+        assert np.array_equal(got["grad_slice"], got["adj_volume"].reshape(-1)[b:e])  # same collective result, own slice
     assert sorted(seen) == list(range(N_VIEWS))
+
+
+def test_shard_bounds_cover_the_parameter_once():
+    for numel, w in [(256 ** 3, 8), (12 ** 3, 2), (10, 4), (3, 8)]:
+        bounds = [multigpu.shard_bounds(numel, r, w) for r in range(w)]
+        assert bounds[0][0] == 0 and bounds[-1][1] == numel
+        assert all(bounds[r][1] == bounds[r + 1][0] for r in range(w - 1))
+        assert all(0 <= e - b <= -(-numel // w) for b, e in bounds)
+    # single process: the slice is the whole parameter
+    t = torch.arange(6.0)
+    full = torch.zeros(6)
+    multigpu.allgather_parameter(full, t)
+    assert torch.equal(full, t) and multigpu.reduce_scatter_gradient(t) is not None
