@@ -577,7 +577,8 @@ class Workspace:
 
 
 def library_path() -> str:
-    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "libdvr_b200.so")
+    """The product library; ``DVR_LIB_PATH`` selects an A/B build of the same sources (csrc/Makefile, measurements only)."""
+    return os.environ.get("DVR_LIB_PATH") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libdvr_b200.so")
 
 
 def load() -> ProductLibrary:

@@ -504,12 +504,23 @@ bool quad_eligible(const Checked& c) {
   return voxels < (1ll << 31) && c.X >= 2 && c.Y >= 2 && c.Z >= 2;
 }
 
+// quads per batch entry of a QUAD buffer: X + 1 slices (the last one duplicates slice X-1, RayInputs::quads)
+long long quad_count(int X, int Y, int Z) { return ((long long)X + 1) * Y * Z; }
+
+void set_quad_indexing(RayInputs& r) {
+  const unsigned YZ = unsigned(r.Y) * unsigned(r.Z);
+  r.quadYZ = YZ;
+  r.quadBias = unsigned(kTwo23Bits) * (YZ + unsigned(r.Z) + 1u);
+  r.quadMax = unsigned(r.X) * YZ - 1u;
+}
+
 // returns the filter id to dispatch on (kFilterTrilinearQuad if a QUAD copy of the volume serves this call)
 int maybe_build_quads(int filter, Checked& c, QuadScratch& q, const CallCtx& ctx, cudaStream_t s) {
   if (filter != DVR_FILTER_TRILINEAR || ctx.layout == 0 || !quad_eligible(c)) return filter;
   const long long voxels = (long long)c.X * c.Y * c.Z;
+  const long long quadsPer = quad_count(c.X, c.Y, c.Z);
   const int nb = c.ri.volB == 0 ? 1 : c.B;
-  const size_t bytes = size_t(voxels) * nb * sizeof(float4);
+  const size_t bytes = size_t(quadsPer) * nb * sizeof(float4);
   // automatic: the copy costs ~5 volume sweeps; worth it once the rays visit about as many cells as there are voxels
   const bool worth = ctx.layout == 1 || (long long)c.B * c.W * c.H * 64 >= voxels * nb;
   float4* quads = nullptr;
@@ -543,7 +554,8 @@ int maybe_build_quads(int filter, Checked& c, QuadScratch& q, const CallCtx& ctx
     quads = q.ptr;
   }
   c.ri.quads = quads;
-  c.ri.quadB = nb == 1 ? 0 : voxels;
+  c.ri.quadB = nb == 1 ? 0 : quadsPer;
+  set_quad_indexing(c.ri);
   return kFilterTrilinearQuad;
 }
 
@@ -701,8 +713,9 @@ int dvr_render_adjoint_ex(const DvrInputs* inputs, const DvrOutputs* fwd, const 
     if (filter == kFilterTrilinearQuad && hasVol) {
       // gradient scratch in the same layout: 2 x red.v4 per cell instead of 8 scalar REDs, folded afterwards
       const long long voxels = (long long)c.X * c.Y * c.Z;
+      const long long quadsPer = quad_count(c.X, c.Y, c.Z);
       ng = aa.avB == 0 ? 1 : c.B;
-      const size_t bytes = size_t(voxels) * ng * sizeof(float4);
+      const size_t bytes = size_t(quadsPer) * ng * sizeof(float4);
       float4* grad = nullptr;
       if (aliased_spatial_strides(adj->adj_volume) || (long long)bytes > ctx.cap) {
         // expanded adj_volume views need the atomics of the in-place path (a fold would lose updates)
@@ -725,7 +738,7 @@ int dvr_render_adjoint_ex(const DvrInputs* inputs, const DvrOutputs* fwd, const 
       }
       if (grad) {
         aa.gradQuads = grad;
-        aa.gradQuadB = ng == 1 ? 0 : voxels;
+        aa.gradQuadB = ng == 1 ? 0 : quadsPer;
       } else {
         g_quad_fallbacks.fetch_add(1, std::memory_order_relaxed);
         filter = inputs->volume_filter_mode;  // no scratch: the in-place path accumulates straight into adj_volume
@@ -1230,7 +1243,7 @@ int dvr_workspace_set_volume(DvrWorkspace* w, const DvrTensor* volume, void* str
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     std::lock_guard<std::mutex> lock(w->m);
     w->quadValid = false;
-    if (!ws_reserve(w->quads, w->quadBytes, size_t(r.X) * r.Y * r.Z * nb * sizeof(float4)))
+    if (!ws_reserve(w->quads, w->quadBytes, size_t(quad_count(r.X, r.Y, r.Z)) * nb * sizeof(float4)))
       fail(DVR_ERR_CUDA, "dvr_workspace_set_volume: out of device memory for the QUAD copy");
     after_launch(launch_build_quads(r, nb, w->quads, s), "dvr_build_quads", s);
     g_quad_builds.fetch_add(1, std::memory_order_relaxed);
@@ -1253,7 +1266,7 @@ int dvr_workspace_begin_volume_gradient(DvrWorkspace* w, const DvrTensor* adj_vo
     std::lock_guard<std::mutex> lock(w->m);
     if (w->accumulating) fail(DVR_ERR_INVALID_ARGUMENT, "a volume-gradient scope is already open on this workspace");
     const long long voxels = (long long)r.X * r.Y * r.Z;
-    const size_t bytes = size_t(voxels) * nb * sizeof(float4);
+    const size_t bytes = size_t(quad_count(r.X, r.Y, r.Z)) * nb * sizeof(float4);
     if (!ws_reserve(w->grad, w->gradBytes, bytes))
       fail(DVR_ERR_CUDA, "dvr_workspace_begin_volume_gradient: out of device memory for the gradient scratch");
     cuda_check(cudaMemsetAsync(w->grad, 0, bytes, s), "dvr_workspace_begin_volume_gradient");
@@ -1281,7 +1294,7 @@ int dvr_workspace_end_volume_gradient(DvrWorkspace* w, const DvrTensor* adj_volu
     aa.adjVolume = static_cast<float*>(adj_volume->ptr);
     aa.avB = r.volB; aa.avx = r.sx; aa.avy = r.sy; aa.avz = r.sz;
     aa.gradQuads = w->grad;
-    aa.gradQuadB = nb == 1 ? 0 : w->adjVoxels;
+    aa.gradQuadB = nb == 1 ? 0 : quad_count(r.X, r.Y, r.Z);
     w->accumulating = false;
     after_launch(launch_fold_quads(r, aa, nb, s), "dvr_fold_quads", s);
     g_folds.fetch_add(1, std::memory_order_relaxed);

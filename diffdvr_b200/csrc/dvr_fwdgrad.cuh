@@ -190,9 +190,8 @@ __global__ void __launch_bounds__(kThreads, N <= 6 ? 4 : 3) k_forward_gradients(
         td.v = t;
         Du<N> fxd = psx + td * pdx, fyd = psy + td * pdy, fzd = psz + td * pdz;
         fxd.v = smp.fx; fyd.v = smp.fy; fzd.v = smp.fz;  // fractional parts share the tangents
-        const float* d = smp.d;
-        dd = du_lerp(du_lerp(du_lerp(d[0], d[4], fxd), du_lerp(d[2], d[6], fxd), fyd),
-                     du_lerp(du_lerp(d[1], d[5], fxd), du_lerp(d[3], d[7], fxd), fyd), fzd);
+        dd = du_lerp(du_lerp(du_lerp(smp.d(0), smp.d(4), fxd), du_lerp(smp.d(2), smp.d(6), fxd), fyd),
+                     du_lerp(du_lerp(smp.d(1), smp.d(5), fxd), du_lerp(smp.d(3), smp.d(7), fxd), fyd), fzd);
       }
       cur = tf_eval_dual<TF, N, HAS_TF>(s_tf, s_dtf, in.R, dd, d0);
     } else {

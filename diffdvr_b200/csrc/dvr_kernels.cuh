@@ -338,16 +338,48 @@ __global__ void __launch_bounds__(kThreads, HAS_RAY ? 6 : 1) k_adjoint(const Ray
       smp.init(in, b, aa.adjVolume, aa.avB);
     // terminationIndex-1 was the last sample that contributed (renderer_kernels.cuh:374-376)
     float fi = float(n - 1);
-    for (int i = n - 1; i >= 0; --i, fi -= 1.0f) {
-      const float t = sample_t(ray, fi);
-      const f3 p = sample_pos<HAS_RAY>(ray, t);
+    // Identity TF: ray constants of blend_adjoint_grey
+    [[maybe_unused]] const float idSa = s_tf[0], idSc = s_tf[1];
+    [[maybe_unused]] const float idKS = (adjAcc.x + adjAcc.y + adjAcc.z) * idSc, idSaStep = idSa * ray.step;
+    // Without position derivatives the sample position needs no t: p_i = (ps + tmin pd) + i (step pd), two hoisted
+    // vectors and one FMA per axis (the forward pass rounds tmin + i step first; the positions agree to an ulp, which
+    // moves the reconstructed densities by ~1e-6 relative, far inside the gradient tolerance).
+    [[maybe_unused]] const f3 p0 = {fmaf(ray.tmin, ray.pd.x, ray.ps.x), fmaf(ray.tmin, ray.pd.y, ray.ps.y),
+                                    fmaf(ray.tmin, ray.pd.z, ray.ps.z)};
+    [[maybe_unused]] const f3 dp = {ray.step * ray.pd.x, ray.step * ray.pd.y, ray.step * ray.pd.z};
+    for (; fi >= 0.f; fi -= 1.0f) {  // fi counts n-1 .. 0 exactly (n < 2^24)
+      float t = 0.f;
+      f3 p;
+      if constexpr (HAS_RAY) {
+        t = sample_t(ray, fi);
+        p = sample_pos<true>(ray, t);
+      } else {
+        const float2 xy = pk_fma(fi, make_float2(dp.x, dp.y), make_float2(p0.x, p0.y));
+        p = {xy.x, xy.y, fmaf(fi, dp.z, p0.z)};
+      }
       const float density = smp.fetch(in, &aa, p.x, p.y, p.z);
-      float tfCache[kRegRows];
-      const f4 cur = tf_eval_cached<TF>(s_tf, in.R, density, tfCache);
-      f4 adjCur;
-      float adjStepBlend;
-      blend_adjoint<BLEND>(acc, adjAcc, cur, ray.step, adjCur, adjStepBlend);
-      const float adjDensity = tf_adjoint<TF, TFACC>(s_tf, in.R, density, adjCur, tfg, tfCache);
+      float adjDensity, adjStepBlend;
+      if constexpr (TF == kTfIdentity) {
+        // r = g = b (renderer_tf.cuh:62-104): one colour lane through the blend inversion and the TF adjoint
+        const float dc = fmaxf(0.f, fminf(density, 1.f));
+        float ak, adjAlphaE;
+        const float adjDc = blend_adjoint_grey<BLEND>(acc.w, adjAcc.w, dc, idKS, idSaStep, ak, adjAlphaE);
+        adjStepBlend = adjAlphaE * (dc * idSa);
+        if constexpr (TFACC == kTfAccReg) {
+          tfg.g[0] = fmaf(adjAlphaE * ray.step, dc, tfg.g[0]);                       // d/d scaleAbsorption
+          tfg.g[1] = fmaf((adjAcc.x + adjAcc.y + adjAcc.z) * ak, dc, tfg.g[1]);      // d/d scaleColor
+        } else if constexpr (TFACC != kTfAccNone) {  // never dispatched (two scalars fit registers); kept correct
+          const float v[2] = {adjAlphaE * ray.step * dc, (adjAcc.x + adjAcc.y + adjAcc.z) * ak * dc};
+          tfg.add_row(0, v);
+        }
+        adjDensity = (density > 0.f && density < 1.f) ? adjDc : 0.f;
+      } else {
+        float tfCache[kRegRows];
+        const f4 cur = tf_eval_cached<TF>(s_tf, in.R, density, tfCache);
+        f4 adjCur;
+        blend_adjoint<BLEND>(acc, adjAcc, cur, ray.step, adjCur, adjStepBlend);
+        adjDensity = tf_adjoint<TF, TFACC>(s_tf, in.R, density, adjCur, tfg, tfCache);
+      }
       const f3 g = smp.template adjoint<HAS_RAY>(adjDensity);
       if constexpr (HAS_RAY) {
         // the reference overwrites its accumulator with the blend term (see compat flag)

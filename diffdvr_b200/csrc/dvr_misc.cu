@@ -82,15 +82,16 @@ __global__ void __launch_bounds__(kThreads) k_count_cells(const RayInputs in, co
   }
 }
 
-// QUAD copy, see RayInputs::quads. One thread per voxel: 4 strided reads (L1/L2 hits after the first touch of
-// a line), one 16-byte write; a streaming pass over 5 x the volume size, ~1 % of a C4 march.
+// QUAD copy, see RayInputs::quads. One thread per quad: 4 strided reads (L1/L2 hits after the first touch of
+// a line), one 16-byte write; a streaming pass over 5 x the volume size. Slice X duplicates slice X-1.
 __global__ void __launch_bounds__(256) k_build_quads(const RayInputs in, float4* quads) {
-  const unsigned n = unsigned(in.X) * unsigned(in.Y) * unsigned(in.Z);
+  const unsigned YZ = unsigned(in.Y) * unsigned(in.Z);
+  const unsigned n = (unsigned(in.X) + 1u) * YZ;
   const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int b = blockIdx.z;
   const unsigned z = i % unsigned(in.Z), xy = i / unsigned(in.Z);
-  const unsigned y = xy % unsigned(in.Y), x = xy / unsigned(in.Y);
+  const unsigned y = xy % unsigned(in.Y), x = min(xy / unsigned(in.Y), unsigned(in.X) - 1u);
   const unsigned y1 = min(y + 1, unsigned(in.Y) - 1), z1 = min(z + 1, unsigned(in.Z) - 1);
   const float* v = in.volume + b * in.volB + (long long)x * in.sx;
   float4 q;
@@ -102,35 +103,41 @@ __global__ void __launch_bounds__(256) k_build_quads(const RayInputs in, float4*
 }
 
 // Folds the QUAD gradient scratch into the caller's adj_volume (accumulating, like the atomics it replaces).
-// Component k of G[x][y][z] targets voxel (x, y + (k>>1 clamped), z + (k&1 clamped)); as a gather per voxel:
-//   .x of (y, z), .y of (y, z-1), .z of (y-1, z), .w of (y-1, z-1), plus the components that the clamp at the
-//   far faces folds back onto the voxel itself (z = Z-1: .y/.w of the same z; y = Y-1: .z/.w of the same y).
+// Component k of G[x][y][z] targets voxel (min(x, X-1), y + (k>>1 clamped), z + (k&1 clamped)); as a gather per voxel
+// and slice: .x of (y, z), .y of (y, z-1), .z of (y-1, z), .w of (y-1, z-1), plus the components that the clamp at
+// the far faces folds back onto the voxel itself (z = Z-1: .y/.w of the same z; y = Y-1: .z/.w of the same y);
+// voxels of the last slice also collect slice X (the x+1 corners of cells on the far x face).
 __global__ void __launch_bounds__(256) k_fold_quads(const RayInputs in, const AdjointArgs aa) {
-  const unsigned n = unsigned(in.X) * unsigned(in.Y) * unsigned(in.Z);
+  const unsigned Z = unsigned(in.Z), Y = unsigned(in.Y), X = unsigned(in.X);
+  const unsigned n = X * Y * Z;
   const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int b = blockIdx.z;
-  const unsigned Z = unsigned(in.Z), Y = unsigned(in.Y);
   const unsigned z = i % Z, xy = i / Z;
   const unsigned y = xy % Y, x = xy / Y;
   const float4* g = aa.gradQuads + (size_t)b * aa.gradQuadB;
   const bool zl = z == Z - 1, yl = y == Y - 1;
-  const float4 q = g[i];
-  float s = q.x;
-  if (zl) s += q.y;
-  if (yl) s += q.z;
-  if (zl && yl) s += q.w;
-  if (z > 0) {
-    const float4 r = g[i - 1];
-    s += r.y;
-    if (yl) s += r.w;
-  }
-  if (y > 0) {
-    const float4 r = g[i - Z];
-    s += r.z;
-    if (zl) s += r.w;
-  }
-  if (y > 0 && z > 0) s += g[i - Z - 1].w;
+  auto gather = [&](unsigned j) {
+    const float4 q = g[j];
+    float s = q.x;
+    if (zl) s += q.y;
+    if (yl) s += q.z;
+    if (zl && yl) s += q.w;
+    if (z > 0) {
+      const float4 r = g[j - 1];
+      s += r.y;
+      if (yl) s += r.w;
+    }
+    if (y > 0) {
+      const float4 r = g[j - Z];
+      s += r.z;
+      if (zl) s += r.w;
+    }
+    if (y > 0 && z > 0) s += g[j - Z - 1].w;
+    return s;
+  };
+  float s = gather(i);
+  if (x == X - 1) s += gather(i + Y * Z);
   if (s != 0.f) {
     float* p = aa.adjVolume + b * aa.avB + (long long)x * aa.avx + (long long)y * aa.avy + (long long)z * aa.avz;
     *p += s;
@@ -143,7 +150,7 @@ cudaError_t launch_fold_quads(const RayInputs& in, const AdjointArgs& aa, int nb
 }
 
 cudaError_t launch_build_quads(const RayInputs& in, int nb, float4* quads, cudaStream_t s) {
-  const unsigned n = unsigned(in.X) * unsigned(in.Y) * unsigned(in.Z);
+  const unsigned n = (unsigned(in.X) + 1u) * unsigned(in.Y) * unsigned(in.Z);
   return launch_kernel(k_build_quads, dim3((n + 255) / 256, 1, nb), 256, 0, s, in, quads);
 }
 

@@ -34,10 +34,14 @@ struct RayInputs {
   const float* volume;
   long long volB;
   int sx, sy, sz;
-  // QUAD copy (kFilterTrilinearQuad): Q[b][x][y][z] = (v[y][z], v[y][z'], v[y'][z], v[y'][z']) of slice x with
-  // y' = min(y+1, Y-1), z' = min(z+1, Z-1): one cell = 2 aligned 16-byte loads (x and min(x+1, X-1))
+  // QUAD copy (kFilterTrilinearQuad): Q[b][x][y][z] = (v[y][z], v[y][z'], v[y'][z], v[y'][z']) of slice min(x, X-1)
+  // for x in [0, X] (X + 1 slices: the far-face clamp of x is a duplicated last slice), y' = min(y+1, Y-1),
+  // z' = min(z+1, Z-1): one cell = 2 aligned 16-byte loads at quad offsets q and q + Y*Z, no clamp in the kernel
   const float4* quads;
-  long long quadB;                   // float4 elements per batch entry (0: one volume for all views)
+  long long quadB;                   // float4 elements per batch entry, (X+1)*Y*Z (0: one volume for all views)
+  // hoisted index arithmetic of the QUAD cell load: q = ux*quadYZ + uy*Z + uz - quadBias on the biased-float bit
+  // patterns of the cell coordinates (dvr_device.cuh load_cell), clamped to quadMax = X*Y*Z - 1 as a safety net
+  unsigned quadYZ, quadBias, quadMax;
   Strided1 boxMin, boxSize;          // p == nullptr -> use the *V value
   float boxMinV[3], boxSizeV[3];
   int cameraMode;
@@ -74,7 +78,7 @@ struct AdjointArgs {
   // kFilterTrilinearQuad + hasVolume: gradients are accumulated into a zeroed QUAD scratch
   // G[b][x][y][z] = (g(y,z), g(y,z'), g(y',z), g(y',z')) with 2 x red.v4 per cell and folded into adjVolume
   // by k_fold_quads afterwards
-  float4* gradQuads;
+  float4* gradQuads;                 // (X+1)*Y*Z quads per batch entry, like RayInputs::quads
   long long gradQuadB;               // float4 elements per batch entry (0: one gradient volume for all views)
   float* adjStep;
   long long asB, asY, asX;

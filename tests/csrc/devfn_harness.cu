@@ -101,6 +101,9 @@ RayInputs volume_inputs(const float* volume, int X, int Y, int Z, const float4* 
   in.volume = volume;
   in.sx = Y * Z; in.sy = Z; in.sz = 1;
   in.quads = quads;
+  in.quadYZ = unsigned(Y) * unsigned(Z);
+  in.quadBias = unsigned(kTwo23Bits) * (in.quadYZ + unsigned(Z) + 1u);
+  in.quadMax = unsigned(X) * in.quadYZ - 1u;
   return in;
 }
 
@@ -113,13 +116,13 @@ __global__ void k_interp(const RayInputs in, int n, const float* pos, float* out
   out[i] = smp.fetch(in, nullptr, pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]);
 }
 
-// adjVolume: n volumes (FILTER = Trilinear: X*Y*Z floats each; TrilinearQuad: X*Y*Z float4 each), zeroed by the caller
+// adjVolume: n volumes (FILTER = Trilinear: X*Y*Z floats each; TrilinearQuad: (X+1)*Y*Z float4 each), zeroed by the caller
 template <int FILTER>
 __global__ void k_interp_adjoint(const RayInputs in, const AdjointArgs aa, int n, const float* pos, const float* g,
                                  float* adjPos, float* adjVolume) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const long long N = (long long)in.X * in.Y * in.Z * (FILTER == kFilterTrilinearQuad ? 4 : 1);
+  const long long N = FILTER == kFilterTrilinearQuad ? (long long)(in.X + 1) * in.Y * in.Z * 4 : (long long)in.X * in.Y * in.Z;
   Sampler<FILTER, true> smp;
   smp.init(in, 0, adjVolume + i * N, 0);
   smp.fetch(in, &aa, pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]);
@@ -184,7 +187,7 @@ DEVFN_API int devfn_tf_adjoint(int32_t mode, int32_t R, int32_t C, const float* 
   return done();
 }
 
-// quads: nullptr = sample the linear volume in place; else the QUAD copy of it (X*Y*Z float4, dvr_misc.cu layout)
+// quads: nullptr = sample the linear volume in place; else the QUAD copy of it ((X+1)*Y*Z float4, dvr_misc.cu layout)
 DEVFN_API int devfn_interp(int32_t X, int32_t Y, int32_t Z, const float* volume, const float* quads, int32_t n,
                            const float* pos, float* out) {
   const RayInputs in = volume_inputs(volume, X, Y, Z, reinterpret_cast<const float4*>(quads));

@@ -80,16 +80,19 @@ class HostFns:
 
 
 def build_quads(volume):
-    """numpy statement of the QUAD copy: Q[x][y][z] = (v[y][z], v[y][z'], v[y'][z], v[y'][z'])
-    with y' = min(y + 1, Y - 1), z' = min(z + 1, Z - 1)."""
+    """numpy statement of the QUAD copy: Q[x][y][z] = (v[y][z], v[y][z'], v[y'][z], v[y'][z']) of
+    slice min(x, X - 1) for x in [0, X] (X + 1 slices), with y' = min(y + 1, Y - 1), z' = min(z + 1, Z - 1)."""
     X, Y, Z = volume.shape
     yp, zp = np.minimum(np.arange(Y) + 1, Y - 1), np.minimum(np.arange(Z) + 1, Z - 1)
     q = np.stack([volume, volume[:, :, zp], volume[:, yp, :], volume[:, yp][:, :, zp]], axis=-1)
+    q = np.concatenate([q, q[-1:]], axis=0)
     return np.ascontiguousarray(q, np.float32)
 
 
 def fold_quads(g):
-    """inverse for gradients: scatter the four components of every quad back onto the voxels they alias"""
+    """inverse for gradients: scatter the four components of every quad back onto the voxels they alias (slice X of the
+    X + 1 slices lands on slice X - 1)"""
+    g = np.concatenate([g[:, :-2], g[:, -2:-1] + g[:, -1:]], axis=1)
     n, X, Y, Z, _ = g.shape
     yp, zp = np.minimum(np.arange(Y) + 1, Y - 1), np.minimum(np.arange(Z) + 1, Z - 1)
     out = np.zeros((n, X, Y, Z), np.float64)
@@ -169,7 +172,7 @@ class DeviceFns:
         v, p, g = self.dev(volume), self.dev(pos), self.dev(g)
         q = self.dev(build_quads(np.asarray(volume, np.float32))) if quad else None
         adj_pos = self.zeros(len(p), 3)
-        adj_vol = self.zeros(len(p), *v.shape, 4) if quad else self.zeros(len(p), *v.shape)
+        adj_vol = self.zeros(len(p), v.shape[0] + 1, *v.shape[1:], 4) if quad else self.zeros(len(p), *v.shape)
         self._call("devfn_interp_adjoint", *v.shape, v, q, len(p), p, g, adj_pos, adj_vol)
         av = adj_vol.cpu().numpy()
         return adj_pos.cpu().numpy(), (fold_quads(av).astype(np.float32) if quad else av)

@@ -39,7 +39,8 @@ def test_cached_copy_is_reused_and_rebuilt_on_demand():
     c2, t2 = render(lib, inp, sc.B, sc.H, sc.W, opts)      # served by the cached copy: one launch
     assert lib.stat("quad_builds") - b0 == 1 and lib.stat("quad_reuses") - r0 == 1
     assert torch.equal(c1, ref_c) and torch.equal(c2, ref_c) and torch.equal(t2, ref_t)
-    assert ws.bytes() == 16 * inp.volume.numel()
+    n = inp.volume.shape[1]
+    assert ws.bytes() == 16 * (n + 1) * n * n       # X + 1 slices: the far-face clamp of x is a duplicated slice
     # contents change under the same pointer: stale until the caller bumps the "version"
     inp.volume.mul_(0.5)
     fresh_c, _ = render(lib, inp, sc.B, sc.H, sc.W, capi.make_call_options(volume_layout=1))
