@@ -340,7 +340,7 @@ __global__ void __launch_bounds__(kThreads, HAS_RAY ? 6 : 1) k_adjoint(const Ray
     float fi = float(n - 1);
     // Identity TF: ray constants of blend_adjoint_grey
     [[maybe_unused]] const float idSa = s_tf[0], idSc = s_tf[1];
-    [[maybe_unused]] const float idKS = (adjAcc.x + adjAcc.y + adjAcc.z) * idSc, idSaStep = idSa * ray.step;
+    [[maybe_unused]] const float idKS = (adjAcc.x + adjAcc.y + adjAcc.z) * idSc;
     // Without position derivatives the sample position needs no t: p_i = (ps + tmin pd) + i (step pd), two hoisted
     // vectors and one FMA per axis (the forward pass rounds tmin + i step first; the positions agree to an ulp, which
     // moves the reconstructed densities by ~1e-6 relative, far inside the gradient tolerance).
@@ -363,7 +363,7 @@ __global__ void __launch_bounds__(kThreads, HAS_RAY ? 6 : 1) k_adjoint(const Ray
         // r = g = b (renderer_tf.cuh:62-104): one colour lane through the blend inversion and the TF adjoint
         const float dc = fmaxf(0.f, fminf(density, 1.f));
         float ak, adjAlphaE;
-        const float adjDc = blend_adjoint_grey<BLEND>(acc.w, adjAcc.w, dc, idKS, idSaStep, ak, adjAlphaE);
+        const float adjDc = blend_adjoint_grey<BLEND>(acc.w, adjAcc.w, dc, idKS, idSa, ray.step, ak, adjAlphaE);
         adjStepBlend = adjAlphaE * (dc * idSa);
         if constexpr (TFACC == kTfAccReg) {
           tfg.g[0] = fmaf(adjAlphaE * ray.step, dc, tfg.g[0]);                       // d/d scaleAbsorption

@@ -28,7 +28,7 @@ def main():
         raise SystemExit(f"{lib} missing: build the CUDA library first (make -C diffdvr_b200/csrc)")
     srcs = [os.path.join(HERE, "renderer.cpp"), os.path.join(HERE, "camera.cpp"), os.path.join(HERE, "tf_utils.cpp"),
             os.path.join(HERE, "volume.cpp"), os.path.join(HERE, "lz4_block.cpp"), os.path.join(HERE, "bindings.cpp")]
-    deps = srcs + [os.path.join(HERE, "renderer.h"), os.path.join(HERE, "camera.h"), os.path.join(HERE, "tf_utils.h"),
+    deps = srcs + [os.path.join(HERE, "renderer.h"), os.path.join(HERE, "kernel_types.h"), os.path.join(HERE, "camera.h"), os.path.join(HERE, "tf_utils.h"),
                    os.path.join(HERE, "volume.h"), os.path.join(HERE, "lz4_block.h"), os.path.join(PKG, "..", "include", "dvr_b200.h"), lib, __file__]
     if os.path.exists(out) and all(os.path.getmtime(out) >= os.path.getmtime(d) for d in deps):
         print("pyrenderer is up to date")

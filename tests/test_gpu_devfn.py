@@ -93,6 +93,11 @@ def test_trilinear_interpolation(quad):
     cases = [(volume, np.concatenate([pos, extra])), (rng.uniform(0, 1, (5, 7, 6)), rng.uniform(-0.5, 7.5, (400, 3)))]
     for vol, p in cases:
         vol, p = vol.astype(np.float32), np.maximum(p, 0.0).astype(np.float32)  # the marcher never samples below 0
+        if quad:
+            # QUAD bakes the far-face clamps into the copy (y' / z' inside the quads, x as the duplicated slice X), so
+            # its contract is what the marcher can produce: box-relative coordinates up to n - 1 plus round-off. The
+            # in-place sampler keeps the reference's per-corner clamps and takes the positions a whole cell outside.
+            p = np.minimum(p, (np.array(vol.shape) - 1) * (1 + 4e-7)).astype(np.float32)
         got = dev.interp(vol, p, quad)
         g = rng.uniform(-1, 1, len(p)).astype(np.float32)
         ap, av = dev.interp_adjoint(vol, p, g, quad)
@@ -108,7 +113,10 @@ def test_quad_layout_is_bit_identical_to_in_place_sampling():
     dev = dc.DeviceFns()
     rng = np.random.RandomState(11)
     vol = rng.uniform(0, 1, (6, 5, 9)).astype(np.float32)
-    p = (rng.uniform(0, 1.05, (2000, 3)) * np.array(vol.shape)).astype(np.float32)
+    # up to the far faces and the round-off beyond them (the marcher's range, see test_trilinear_interpolation)
+    far = (np.array(vol.shape) - 1) * (1 + 4e-7)
+    p = np.minimum(rng.uniform(0, 1.05, (2000, 3)) * np.array(vol.shape), far).astype(np.float32)
+    assert (p > np.array(vol.shape) - 1).any()
     assert np.array_equal(dev.interp(vol, p, False), dev.interp(vol, p, True))
     g = rng.uniform(-1, 1, len(p)).astype(np.float32)
     (ap0, av0), (ap1, av1) = dev.interp_adjoint(vol, p, g, False), dev.interp_adjoint(vol, p, g, True)
