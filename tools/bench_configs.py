@@ -5,6 +5,7 @@ in a workspace (built once, outside the timed region; the adjoint's gradient scr
 Prints one JSON object per config; `--out` also writes a markdown table. `DVR_LIB_PATH` selects an A/B build.
 
     python tools/bench_configs.py [--configs C1,C2,C3,C4,C5] [--reps 5] [--out profiles/rNN_configs.md]
+    ncu --set full -k regex:'k_adjoint|k_forward|k_fwdgrad' ... python tools/bench_configs.py --profile
 """
 from __future__ import annotations
 
@@ -22,8 +23,11 @@ import torch  # noqa: E402
 from diffdvr_b200 import capi, workloads  # noqa: E402
 
 
+WARMUP = 2
+
+
 def timed(fn, reps, flush):
-    for _ in range(2):
+    for _ in range(WARMUP):
         fn()
     ms = []
     for _ in range(reps):
@@ -94,7 +98,12 @@ def main():
     ap.add_argument("--configs", default="C1,C2,C3,C4,C5")
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--out", default=None)
+    ap.add_argument("--profile", action="store_true",
+                    help="launch every kernel exactly once (no warm-up, one repetition): the run to put under ncu")
     a = ap.parse_args()
+    if a.profile:
+        global WARMUP
+        WARMUP, a.reps = 0, 1
     assert torch.cuda.is_available(), "needs a CUDA device (no CPU fallback)"
     flush = torch.empty(256 * 1024 * 1024 // 4, device="cuda")
     rows = []
