@@ -60,9 +60,12 @@ def test_forward_and_adjoint_are_the_c_abi_results(shim, camera_mode, tf_mode):
         bufs["adj_camera_ray_start"] = torch.zeros(B, H, W, 3, device="cuda")
         bufs["adj_camera_ray_dir"] = torch.zeros(B, H, W, 3, device="cuda")
     adj = capi.make_adjoint_outputs(**bufs)
-    fwd = capi.make_outputs(torch.from_numpy(want_c).cuda(), torch.from_numpy(want_t).cuda())
-    ac = capi.tensor_view(torch.from_numpy(adj_color).cuda())
-    keep = (fwd, ac)
+    # DvrTensor views do not own their tensors: keep the device copies alive until the call has run
+    color_in, term_in, adj_color_in = torch.from_numpy(want_c).cuda(), torch.from_numpy(want_t).cuda(), \
+        torch.from_numpy(adj_color).cuda()
+    fwd = capi.make_outputs(color_in, term_in)
+    ac = capi.tensor_view(adj_color_in)
+    keep = (fwd, ac, color_in, term_in, adj_color_in)
     assert shim.shim_render_adjoint(ctypes.byref(c_in), ctypes.byref(fwd), ctypes.byref(ac), ctypes.byref(adj),
                                     _stream()) == 1, shim.shim_last_error()
     torch.cuda.synchronize()
