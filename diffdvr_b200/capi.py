@@ -89,8 +89,11 @@ class DvrAdjointOutputs(ctypes.Structure):
     ]
 
 
+ABI_VERSION = 3  # include/dvr_b200.h DVR_ABI_VERSION
+
+
 class DvrCallOptions(ctypes.Structure):
-    """include/dvr_b200.h DvrCallOptions (ABI version 2)."""
+    """include/dvr_b200.h DvrCallOptions (ABI version 3)."""
     _fields_ = [
         ("struct_size", ctypes.c_uint32),
         ("volume_layout", ctypes.c_int32),
@@ -98,11 +101,13 @@ class DvrCallOptions(ctypes.Structure):
         ("sync", ctypes.c_int32),
         ("max_scratch_bytes", ctypes.c_int64),
         ("workspace", ctypes.c_void_p),
+        ("forward_mode_tf", ctypes.c_int32),
+        ("reserved0", ctypes.c_int32),
     ]
 
 
 def make_call_options(volume_layout: int = -1, compat_stepsize_overwrite: bool = False, sync: bool = False,
-                      max_scratch_bytes: int = 0, workspace=None) -> DvrCallOptions:
+                      max_scratch_bytes: int = 0, workspace=None, forward_mode_tf: int = 0) -> DvrCallOptions:
     o = DvrCallOptions()
     o.struct_size = ctypes.sizeof(DvrCallOptions)
     o.volume_layout = int(volume_layout)
@@ -110,6 +115,7 @@ def make_call_options(volume_layout: int = -1, compat_stepsize_overwrite: bool =
     o.sync = int(bool(sync))
     o.max_scratch_bytes = int(max_scratch_bytes)
     o.workspace = workspace.handle if workspace is not None else None
+    o.forward_mode_tf = int(forward_mode_tf)   # 1: the slot-major ceil(D/8)-pass kernel (A/B measurements)
     o._keep = workspace
     return o
 
@@ -411,6 +417,9 @@ class ProductLibrary(Library):
         L.dvr_has_variant.argtypes = [ctypes.c_int32] * 4
         L.dvr_abi_version.restype = ctypes.c_int32
         L.dvr_abi_version.argtypes = []
+        if L.dvr_abi_version() != ABI_VERSION:   # the struct mirrors above are those of ONE header version
+            raise RuntimeError(f"{path}: ABI version {L.dvr_abi_version()}, this module mirrors version {ABI_VERSION} "
+                               "(rebuild with __graft_entry__.build())")
         L.dvr_count_cell_visits.restype = ctypes.c_int
         L.dvr_count_cell_visits.argtypes = [ctypes.POINTER(DvrInputs), ctypes.POINTER(DvrTensor), ctypes.c_void_p,
                                             ctypes.c_void_p]

@@ -1,7 +1,7 @@
 // Instances of the adjoint kernel for ONE (tf, blend) pair, selected with -DDVR_TF=.. -DDVR_BL=..
 // (one translation unit per pair so the ~20 instances per pair compile in parallel).
-// Flags: hasVol x {no TF grad, register TF grad, shared-memory TF grad} x hasRay
-// (hasRay = stepsize and/or camera adjoints; which of the two are written is a run-time flag).
+// Flags: hasVol x {no TF grad, register TF grad, shared-memory TF grad} x {no ray gradients, stepsize only, camera
+// (+ stepsize as a run-time flag)}.
 #include "dvr_kernels.cuh"
 #include "dvr_launch.h"
 
@@ -13,22 +13,29 @@
 
 namespace dvr {
 
-template <int F, bool V, int A, bool R>
+template <int F, bool V, int A, int R>
 static cudaError_t go(const RayInputs& in, const AdjointArgs& aa, dim3 grid, size_t smem, cudaStream_t s) {
-  if constexpr (!V && A == kTfAccNone && !R) {
+  if constexpr (!V && A == kTfAccNone && R == kRayNone) {
     return kErrNoInstance;  // nothing to compute
   } else if constexpr (DVR_TF == kTfIdentity && A == kTfAccSmem) {
     return kErrNoInstance;  // the 2-entry identity table always lives in registers
+  } else if constexpr ((DVR_TF == kTfTexture || DVR_TF == kTfLinear) && A == kTfAccReg) {
+    return kErrNoInstance;  // two-row TFs always use the row window + per-warp shared table (tfacc_for)
   } else {
     return launch_kernel(k_adjoint<F, DVR_TF, DVR_BL, V, A, R>, grid, kThreads, smem, s, in, aa);
   }
 }
 template <int F, bool V, int A>
-static cudaError_t by_ray(bool r, const RayInputs& in, const AdjointArgs& aa, dim3 g, size_t sm, cudaStream_t s) {
-  return r ? go<F, V, A, true>(in, aa, g, sm, s) : go<F, V, A, false>(in, aa, g, sm, s);
+static cudaError_t by_ray(int r, const RayInputs& in, const AdjointArgs& aa, dim3 g, size_t sm, cudaStream_t s) {
+  switch (r) {
+    case kRayNone: return go<F, V, A, kRayNone>(in, aa, g, sm, s);
+    case kRayStep: return go<F, V, A, kRayStep>(in, aa, g, sm, s);
+    case kRayCam: return go<F, V, A, kRayCam>(in, aa, g, sm, s);
+    default: return kErrNoInstance;
+  }
 }
 template <int F, bool V>
-static cudaError_t by_acc(int a, bool r, const RayInputs& in, const AdjointArgs& aa, dim3 g, size_t sm, cudaStream_t s) {
+static cudaError_t by_acc(int a, int r, const RayInputs& in, const AdjointArgs& aa, dim3 g, size_t sm, cudaStream_t s) {
   switch (a) {
     case kTfAccNone: return by_ray<F, V, kTfAccNone>(r, in, aa, g, sm, s);
     case kTfAccReg: return by_ray<F, V, kTfAccReg>(r, in, aa, g, sm, s);
@@ -37,17 +44,17 @@ static cudaError_t by_acc(int a, bool r, const RayInputs& in, const AdjointArgs&
   }
 }
 
-cudaError_t DVR_NAME(DVR_TF, DVR_BL)(int filter, bool hasVol, int tfacc, bool hasRay, const RayInputs& in,
+cudaError_t DVR_NAME(DVR_TF, DVR_BL)(int filter, bool hasVol, int tfacc, int ray, const RayInputs& in,
                                      const AdjointArgs& aa, dim3 grid, size_t smem, cudaStream_t s) {
   if (filter == kFilterNearest)
-    return hasVol ? by_acc<kFilterNearest, true>(tfacc, hasRay, in, aa, grid, smem, s)
-                  : by_acc<kFilterNearest, false>(tfacc, hasRay, in, aa, grid, smem, s);
+    return hasVol ? by_acc<kFilterNearest, true>(tfacc, ray, in, aa, grid, smem, s)
+                  : by_acc<kFilterNearest, false>(tfacc, ray, in, aa, grid, smem, s);
   if (filter == kFilterTrilinear)
-    return hasVol ? by_acc<kFilterTrilinear, true>(tfacc, hasRay, in, aa, grid, smem, s)
-                  : by_acc<kFilterTrilinear, false>(tfacc, hasRay, in, aa, grid, smem, s);
+    return hasVol ? by_acc<kFilterTrilinear, true>(tfacc, ray, in, aa, grid, smem, s)
+                  : by_acc<kFilterTrilinear, false>(tfacc, ray, in, aa, grid, smem, s);
   if (filter == kFilterTrilinearQuad)
-    return hasVol ? by_acc<kFilterTrilinearQuad, true>(tfacc, hasRay, in, aa, grid, smem, s)
-                  : by_acc<kFilterTrilinearQuad, false>(tfacc, hasRay, in, aa, grid, smem, s);
+    return hasVol ? by_acc<kFilterTrilinearQuad, true>(tfacc, ray, in, aa, grid, smem, s)
+                  : by_acc<kFilterTrilinearQuad, false>(tfacc, ray, in, aa, grid, smem, s);
   return kErrNoInstance;
 }
 

@@ -6,6 +6,7 @@
 #include <atomic>
 #include <cmath>
 #include <cstdarg>
+#include <cstddef>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -30,6 +31,7 @@ struct CallCtx {
   int compat = 0;
   long long cap = 16ll << 30;
   DvrWorkspace* ws = nullptr;
+  bool fwdTfSlotMajor = false;
 };
 
 struct Fail {
@@ -79,9 +81,15 @@ CallCtx resolve_options(const DvrCallOptions* o) {
   CallCtx c;
   t_call_sync = 0;
   if (!o) return c;
-  if (o->struct_size < sizeof(DvrCallOptions))
+  // ABI 2.0 shipped a 32-byte struct (up to `workspace`); later fields are read only when struct_size covers them
+  if (o->struct_size < offsetof(DvrCallOptions, workspace) + sizeof(void*))
     fail(DVR_ERR_INVALID_ARGUMENT, "DvrCallOptions::struct_size is %u, expected %zu (use dvr_call_options_init)",
          o->struct_size, sizeof(DvrCallOptions));
+  if (o->struct_size >= offsetof(DvrCallOptions, forward_mode_tf) + sizeof(int32_t)) {
+    if (o->forward_mode_tf < 0 || o->forward_mode_tf > 1)
+      fail(DVR_ERR_INVALID_ARGUMENT, "forward_mode_tf must be 0 or 1, but is %d", o->forward_mode_tf);
+    c.fwdTfSlotMajor = o->forward_mode_tf == 1;
+  }
   if (o->volume_layout < -1 || o->volume_layout > 1)
     fail(DVR_ERR_INVALID_ARGUMENT, "volume_layout must be -1, 0 or 1, but is %d", o->volume_layout);
   c.layout = o->volume_layout;
@@ -588,10 +596,10 @@ bool aliased_spatial_strides(const DvrTensor& t) {
 
 namespace dvr {
 
-cudaError_t launch_adjoint(int filter, int tf, int blend, bool hasVol, int tfacc, bool hasRay, const RayInputs& in,
+cudaError_t launch_adjoint(int filter, int tf, int blend, bool hasVol, int tfacc, int ray, const RayInputs& in,
                            const AdjointArgs& aa, dim3 grid, size_t smem, cudaStream_t s) {
 #define DVR_CASE(TF, BL) \
-  if (tf == TF && blend == BL) return launch_adjoint_##TF##_##BL(filter, hasVol, tfacc, hasRay, in, aa, grid, smem, s);
+  if (tf == TF && blend == BL) return launch_adjoint_##TF##_##BL(filter, hasVol, tfacc, ray, in, aa, grid, smem, s);
   DVR_FOR_EACH_ADJOINT_INSTANCE(DVR_CASE)
 #undef DVR_CASE
   return kErrNoInstance;
@@ -701,7 +709,13 @@ int dvr_render_adjoint_ex(const DvrInputs* inputs, const DvrOutputs* fwd, const 
     }
     const int tf = inputs->tf_mode;
     int tfacc = kTfAccNone;
-    if (hasTf) tfacc = (tf == kTfIdentity || c.ri.R <= kRegRows) ? kTfAccReg : kTfAccSmem;
+    // Texture / Linear touch two neighbouring rows per sample: a two-row register window flushed into a per-warp
+    // shared table, whatever R. Identity / Gaussian touch every row: register accumulators while they fit.
+    if (hasTf) {
+      if (tf == kTfTexture || tf == kTfLinear) tfacc = kTfAccSmem;
+      else tfacc = (tf == kTfIdentity || c.ri.R <= kRegRows) ? kTfAccReg : kTfAccSmem;
+    }
+    const int rayMode = aa.hasCam ? kRayCam : (aa.hasStep ? kRayStep : kRayNone);
     const int entries = c.ri.R * tf_channels(tf);
     const int ntab = tfacc == kTfAccSmem ? kThreads / 32 : (tfacc == kTfAccReg ? 1 : 0);
     const size_t smem =
@@ -744,7 +758,7 @@ int dvr_render_adjoint_ex(const DvrInputs* inputs, const DvrOutputs* fwd, const 
         filter = inputs->volume_filter_mode;  // no scratch: the in-place path accumulates straight into adj_volume
       }
     }
-    after_launch(launch_adjoint(filter, tf, inputs->blend_mode, hasVol, tfacc, hasRay, c.ri, aa,
+    after_launch(launch_adjoint(filter, tf, inputs->blend_mode, hasVol, tfacc, rayMode, c.ri, aa,
                                 tile_grid(c), smem, s),
                  "dvr_render_adjoint", s);
     if (fold) {
@@ -801,6 +815,9 @@ int dvr_render_forward_gradients_ex(const DvrInputs* inputs, const DvrForwardDif
     ga.grad = static_cast<float*>(gradients_out->ptr);
     ga.gB = gradients_out->stride[0]; ga.gY = gradients_out->stride[1]; ga.gX = gradients_out->stride[2];
     ga.gD = gradients_out->stride[3]; ga.gC = gradients_out->stride[4];
+    // the four channels of a Jacobian slot as one 16-byte access where the layout allows it
+    ga.gradVec4 = ga.gC == 1 && ga.gD % 4 == 0 && ga.gX % 4 == 0 && ga.gY % 4 == 0 && ga.gB % 4 == 0 &&
+                  (reinterpret_cast<uintptr_t>(ga.grad) & 15) == 0;
     const int tf = inputs->tf_mode;
     const size_t smem = check_smem(size_t(((c.ri.R * tf_row(tf) + 3) & ~3) + c.ri.R * tf_row(tf)) * sizeof(float));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -816,7 +833,37 @@ int dvr_render_forward_gradients_ex(const DvrInputs* inputs, const DvrForwardDif
                    "dvr_render_forward_gradients", s);
       return;
     }
-    // TF tangents: ceil(D / chunk) marching passes over disjoint slot ranges
+    if (!ctx.fwdTfSlotMajor && (tf == kTfIdentity || tf == kTfTexture || tf == kTfLinear)) {
+      // TF tangents of a two-row (or scalar) table: ONE sample-major pass for any D (dvr_tfjac.cuh). It needs the
+      // final pixel values, so the colour comes first: from the input-major pass when ray / stepsize tangents are
+      // traced as well (it writes all D slots, zeros where no input maps), else from the plain forward kernel
+      // followed by a zero-fill of the Jacobian.
+      ga.d0 = 0;
+      ga.writeColor = 1;
+      if (hasStep || hasCam) {
+        after_launch(launch_forward_gradients(filter, tf, inputs->blend_mode, 0, true, false, c.ri, fo, ga,
+                                              tile_grid(c), smem, s),
+                     "dvr_render_forward_gradients", s);
+      } else {
+        after_launch(launch_forward(filter, tf, inputs->blend_mode, c.ri, fo, tile_grid(c), smem, s),
+                     "dvr_render_forward_gradients", s);
+        const long long D4 = 4ll * st->D;
+        const bool dense = ga.gC == 1 && ga.gD == 4 && ga.gX == D4 && ga.gY == D4 * c.W &&
+                           (c.B == 1 || ga.gB == D4 * c.W * c.H);
+        if (dense) {
+          cuda_check(cudaMemsetAsync(ga.grad, 0, size_t(D4) * c.W * c.H * c.B * sizeof(float), s),
+                     "dvr_render_forward_gradients");
+        } else {
+          after_launch(launch_zero_jacobian(ga, c.W, c.H, c.B, s), "dvr_render_forward_gradients", s);
+        }
+      }
+      ga.exactPos = hasStep || hasCam;
+      after_launch(launch_forward_gradients(filter, tf, inputs->blend_mode, -1, hasStep || hasCam, true, c.ri, fo, ga,
+                                            tile_grid(c), smem, s),
+                   "dvr_render_forward_gradients", s);
+      return;
+    }
+    // TF tangents, slot-major: ceil(D / chunk) marching passes over disjoint slot ranges
     int d0 = 0;
     while (d0 < st->D) {
       const int left = st->D - d0;

@@ -74,6 +74,16 @@ template <int N> DVR_DEV Du<N> du_lerp(float a, float b, float t) { return du_co
 
 template <int N> struct Du4 { Du<N> x, y, z, w; };
 
+// four channels of a pixel / Jacobian slot: one STG.128 when the layout allows it (vec4: channel stride 1, 16-byte
+// aligned), else four strided stores
+DVR_DEV void store4(float* p, long long cs, int vec4, float a, float b, float c, float d) {
+  if (vec4) {
+    *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+  } else {
+    p[0] = a; p[cs] = b; p[2 * cs] = c; p[3 * cs] = d;
+  }
+}
+
 // TF evaluation in dual numbers (renderer_tf.cuh:121-154, 255-288, 436-485, 521-560).
 // DENS is float (no positional tangents) or Du<N>. s_dtf mirrors s_tf's layout with the
 // tangent slot of every TF entry (or is unused when !HAS_TF).
@@ -239,18 +249,14 @@ __global__ void __launch_bounds__(kThreads, N <= 6 ? 4 : 3) k_forward_gradients(
     }
   }
   if (ga.writeColor) {
-    float* c = out.color + b * out.cB + y * out.cY + x * out.cX;
-    c[0] = acc.x.v; c[out.cC] = acc.y.v; c[2 * out.cC] = acc.z.v; c[3 * out.cC] = acc.w.v;
+    store4(out.color + b * out.cB + y * out.cY + x * out.cX, out.cC, out.colorVec4, acc.x.v, acc.y.v, acc.z.v, acc.w.v);
     out.term[b * out.tB + y * out.tY + x * out.tX] = i;
   }
   float* g = ga.grad + b * ga.gB + y * ga.gY + x * ga.gX;
 #pragma unroll
   for (int k = 0; k < N; ++k) {
     const int d = d0 + k;
-    if (d < ga.D) {
-      float* gd = g + d * ga.gD;
-      gd[0] = acc.x.d[k]; gd[ga.gC] = acc.y.d[k]; gd[2 * ga.gC] = acc.z.d[k]; gd[3 * ga.gC] = acc.w.d[k];
-    }
+    if (d < ga.D) store4(g + d * ga.gD, ga.gC, ga.gradVec4, acc.x.d[k], acc.y.d[k], acc.z.d[k], acc.w.d[k]);
   }
 }
 
@@ -312,8 +318,8 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
       for (int r = 0; r < in.R; ++r) {
         const float* row = s_tf + 8 * r;
         const f4 ci = lds4(row);
-        const float n = gauss_exp(gauss_arg(density, row));
-        const float k = n * div_rcp(row[4] - density, row[5] * row[5], row[7]);
+        const float n = gauss_exp(gauss_arg<false>(density, row));
+        const float k = n * gauss_slope(density, row);
         cv.x = fmaf(ci.x, n, cv.x); cv.y = fmaf(ci.y, n, cv.y); cv.z = fmaf(ci.z, n, cv.z); cv.w = fmaf(ci.w, n, cv.w);
         cs.x = fmaf(ci.x, k, cs.x); cs.y = fmaf(ci.y, k, cs.y); cs.z = fmaf(ci.z, k, cs.z); cs.w = fmaf(ci.w, k, cs.w);
       }
@@ -357,8 +363,7 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
     acc.z = fmaf(om * cv.z, av, acc.z);
     acc.w = fmaf(om, av, acc.w);
   }
-  float* c = out.color + b * out.cB + y * out.cY + x * out.cX;
-  c[0] = acc.x; c[out.cC] = acc.y; c[2 * out.cC] = acc.z; c[3 * out.cC] = acc.w;
+  store4(out.color + b * out.cB + y * out.cY + x * out.cX, out.cC, out.colorVec4, acc.x, acc.y, acc.z, acc.w);
   out.term[b * out.tB + y * out.tY + x * out.tX] = i;
   // slots <- inputs
   float* g = ga.grad + b * ga.gB + y * ga.gY + x * ga.gX;
@@ -369,8 +374,7 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
       const int slot = j < 3 ? ga.dRayStart[j] : (j < 6 ? ga.dRayDir[j - 3] : ga.dStep);
       if (slot == d) { gx += ax[j]; gy += ay[j]; gz += az[j]; gw += aw[j]; }
     }
-    float* gd = g + d * ga.gD;
-    gd[0] = gx; gd[ga.gC] = gy; gd[2 * ga.gC] = gz; gd[3 * ga.gC] = gw;
+    store4(g + d * ga.gD, ga.gC, ga.gradVec4, gx, gy, gz, gw);
   }
 }
 

@@ -1,6 +1,8 @@
 // Instances of the forward-mode kernel for ONE (tf, blend) pair (-DDVR_TF=.. -DDVR_BL=..):
-// {Nearest, Trilinear, Trilinear on the QUAD copy} x ({input-major} + chunk {1, 6, 8} x {tf, pos+tf}).
+// {Nearest, Trilinear, Trilinear on the QUAD copy} x ({input-major} + {sample-major TF Jacobian} + chunk {1, 6, 8} x
+// {tf, pos+tf}).
 #include "dvr_fwdgrad.cuh"
+#include "dvr_tfjac.cuh"
 #include "dvr_launch.h"
 
 #ifndef DVR_TF
@@ -23,6 +25,13 @@ template <int F>
 static cudaError_t by_chunk(int n, bool p, bool t, const RayInputs& in, const ForwardOutputs& out,
                             const ForwardGradArgs& ga, dim3 g, size_t sm, cudaStream_t s) {
   switch (n) {
+    case -1:  // sample-major single pass: TF tangents of Identity / Texture / Linear tables (k_tf_jacobian)
+      if constexpr (DVR_TF == kTfIdentity || DVR_TF == kTfTexture || DVR_TF == kTfLinear) {
+        if (!t) return kErrNoInstance;
+        return launch_kernel(k_tf_jacobian<F, DVR_TF, DVR_BL>, g, kThreads, sm, s, in, out, ga);
+      } else {
+        return kErrNoInstance;
+      }
     case 0:  // input-major single pass: ray / stepsize tangents only (k_forward_gradients_inputs)
       if (!p || t) return kErrNoInstance;
       return launch_kernel(k_forward_gradients_inputs<F, DVR_TF, DVR_BL>, g, kThreads, sm, s, in, out, ga);

@@ -87,30 +87,56 @@ template <int TF, int TFACC>
 struct TfGrad {
   static constexpr int CH = TfChannels<TF>::v;
   static constexpr int NREG = TFACC == kTfAccReg ? kRegRows * CH : 1;
+  static constexpr int kNoBase = -0x40000000;
   float g[NREG];     // kTfAccReg: whole table; indexing is fully unrolled (stays in registers)
-  float row[2][CH];  // kTfAccSmem (Texture/Linear): cached rows base, base+1
+  float row[2][CH];  // kTfAccSmem (Texture/Linear): the two rows the ray is currently between
+  // kTfAccSmem window key. Texture: floor of the texture coordinate, -1 .. R (the rows are min(max(base, 0), R-1) and
+  // min(max(base + 1, 0), R-1): below the first / above the last texel centre both are the same clamped row);
+  // Linear: the interval index (rows base, base + 1)
   int base;
+  int rows;          // R
   float* table;      // kTfAccSmem: this warp's table
 
-  DVR_DEV void init(float* warpTable) {
+  DVR_DEV void init(float* warpTable, int R) {
 #pragma unroll
     for (int i = 0; i < NREG; ++i) g[i] = 0.f;
 #pragma unroll
     for (int c = 0; c < CH; ++c) row[0][c] = row[1][c] = 0.f;
-    base = -2;  // never aliases a valid row or row-1
+    base = kNoBase;
+    rows = R;
     table = warpTable;
   }
   DVR_DEV void flush_rows() {
-    if (base >= 0) {
+    if (base != kNoBase) {
+      int r0 = base, r1 = base + 1;
+      if constexpr (TF == kTfTexture) {
+        r0 = min(max(r0, 0), rows - 1);
+        r1 = min(max(r1, 0), rows - 1);
+      }
 #pragma unroll
       for (int c = 0; c < CH; ++c) {
-        if (row[0][c] != 0.f) atomicAdd(table + base * CH + c, row[0][c]);
-        if (row[1][c] != 0.f) atomicAdd(table + (base + 1) * CH + c, row[1][c]);
+        if (row[0][c] != 0.f) atomicAdd(table + r0 * CH + c, row[0][c]);
+        if (row[1][c] != 0.f) atomicAdd(table + r1 * CH + c, row[1][c]);
         row[0][c] = row[1][c] = 0.f;
       }
     }
   }
-  // contribution v[0..CH) to row r (two-row modes call this with r = i and r = i or i+1)
+  // kTfAccSmem, Texture / Linear: the sample lies between rows (key, key + 1) with weights (1 - w, w); v = adjoint of
+  // the interpolated value. One compare per sample, the products fused into the accumulation (the reference: 8
+  // global atomics per sample, renderer_tf.cuh:208-216).
+  DVR_DEV void add_pair(int key, const float* v, float w) {
+    if (key != base) {
+      flush_rows();
+      base = key;
+    }
+    const float w0 = 1.f - w;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      row[0][c] = fmaf(v[c], w0, row[0][c]);
+      row[1][c] = fmaf(v[c], w, row[1][c]);
+    }
+  }
+  // contribution v[0..CH) to row r (register accumulators, or straight into the shared table)
   DVR_DEV void add_row(int r, const float* v) {
     if constexpr (TFACC == kTfAccReg) {
 #pragma unroll
@@ -119,18 +145,6 @@ struct TfGrad {
 #pragma unroll
           for (int c = 0; c < CH; ++c) g[rr * CH + c] += v[c];
         }
-    } else if constexpr (TF == kTfTexture || TF == kTfLinear) {
-      if (r != base && r != base + 1) {  // only the first of the two calls can miss
-        flush_rows();
-        base = r;
-      }
-      if (r == base) {
-#pragma unroll
-        for (int c = 0; c < CH; ++c) row[0][c] += v[c];
-      } else {
-#pragma unroll
-        for (int c = 0; c < CH; ++c) row[1][c] += v[c];
-      }
     } else {
 #pragma unroll
       for (int c = 0; c < CH; ++c) atomicAdd(table + r * CH + c, v[c]);
@@ -138,36 +152,59 @@ struct TfGrad {
   }
 };
 
-// adjoint of tf_eval; returns adj_density and adds the parameter adjoints to `acc`
-// Gaussian TF: the adjoint needs the same exp(-(d-mu)^2 / 2 sigma^2) per row as the evaluation; the first
-// kRegRows of them are kept in registers between the two (the precise expf is ~10 instructions).
+// What the evaluation of a sample leaves behind for its adjoint (evaluated back to back in the adjoint kernel):
+//   Gaussian: exp(-(d-mu)^2 / 2 sigma^2) of the first kRegRows rows; Texture / Linear: the row pair, the interpolation
+//   weight and v1 - v0 (the table is not read twice and the coordinates are not computed twice).
+template <int TF> struct TfCache { float ni[kRegRows]; };
+template <> struct TfCache<kTfTexture> { int fl; float df; f4 dv; };
+template <> struct TfCache<kTfLinear> { int i; float frac, d2, p0, p1, rcp; f4 dv; };
+
 template <int TF>
-DVR_DEV f4 tf_eval_cached(const float* s_tf, int R, float density, float (&ni)[kRegRows]) {
+DVR_DEV f4 tf_eval_cached(const float* s_tf, int R, float density, TfCache<TF>& cache) {
   if constexpr (TF == kTfGaussian) {
+    float (&ni)[kRegRows] = cache.ni;
     f4 c = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int i = 0; i < kRegRows; ++i) {
       ni[i] = 0.f;
       if (i < R) {
         const f4 ci = lds4(s_tf + 8 * i);
-        ni[i] = gauss_exp(gauss_arg(density, s_tf + 8 * i));
+        ni[i] = gauss_exp(gauss_arg<false>(density, s_tf + 8 * i));
         c.x = fmaf(ci.x, ni[i], c.x); c.y = fmaf(ci.y, ni[i], c.y); c.z = fmaf(ci.z, ni[i], c.z); c.w = fmaf(ci.w, ni[i], c.w);
       }
     }
     for (int i = kRegRows; i < R; ++i) {
       const f4 ci = lds4(s_tf + 8 * i);
-      const float n = gauss_exp(gauss_arg(density, s_tf + 8 * i));
+      const float n = gauss_exp(gauss_arg<false>(density, s_tf + 8 * i));
       c.x = fmaf(ci.x, n, c.x); c.y = fmaf(ci.y, n, c.y); c.z = fmaf(ci.z, n, c.z); c.w = fmaf(ci.w, n, c.w);
     }
     return c;
+  } else if constexpr (TF == kTfTexture) {  // tf_eval, keeping the coordinates and v1 - v0
+    int i0, i1;
+    texture_coords(density, R, i0, i1, cache.df, cache.fl);
+    const f4 v0 = lds4(s_tf + 4 * i0), v1 = lds4(s_tf + 4 * i1);
+    cache.dv = {v1.x - v0.x, v1.y - v0.y, v1.z - v0.z, v1.w - v0.w};
+    const float df = cache.df;
+    return {fmaf(df, cache.dv.x, v0.x), fmaf(df, cache.dv.y, v0.y), fmaf(df, cache.dv.z, v0.z), fmaf(df, cache.dv.w, v0.w)};
+  } else if constexpr (TF == kTfLinear) {
+    const int i = linear_interval(s_tf, R, density);
+    const f4 v0 = lds4(s_tf + 8 * i), v1 = lds4(s_tf + 8 * (i + 1));
+    cache.i = i;
+    cache.p0 = s_tf[8 * i + 4]; cache.p1 = s_tf[8 * (i + 1) + 4]; cache.rcp = s_tf[8 * i + 5];
+    cache.d2 = fmaxf(cache.p0, fminf(density, cache.p1));
+    cache.frac = div_rcp(cache.d2 - cache.p0, cache.p1 - cache.p0, cache.rcp);
+    cache.dv = {v1.x - v0.x, v1.y - v0.y, v1.z - v0.z, v1.w - v0.w};
+    const float f = cache.frac;
+    return {fmaf(f, cache.dv.x, v0.x), fmaf(f, cache.dv.y, v0.y), fmaf(f, cache.dv.z, v0.z), fmaf(f, cache.dv.w, v0.w)};
   } else {
     return tf_eval<TF>(s_tf, R, density);
   }
 }
 
+// adjoint of tf_eval; returns adj_density and adds the parameter adjoints to `acc`
 template <int TF, int TFACC>
 DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC, TfGrad<TF, TFACC>& acc,
-                         const float (&cache)[kRegRows]) {
+                         const TfCache<TF>& cache) {
   constexpr bool HAS_TF = TFACC != kTfAccNone;
   if constexpr (TF == kTfIdentity) {  // renderer_tf.cuh:75-104
     const float dc = fmaxf(0.f, fminf(density, 1.f));
@@ -182,12 +219,14 @@ DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC
     }
     return (density > 0.f && density < 1.f) ? adjDc : 0.f;
   } else if constexpr (TF == kTfTexture) {  // :173-220
-    int i0, i1;
-    float df;
-    texture_coords(density, R, i0, i1, df);
-    const f4 v0 = lds4(s_tf + 4 * i0), v1 = lds4(s_tf + 4 * i1);
-    const float adjDf = dot4(adjC, f4{v1.x - v0.x, v1.y - v0.y, v1.z - v0.z, v1.w - v0.w});
-    if constexpr (HAS_TF) {
+    const int fl = cache.fl;
+    const float df = cache.df;
+    const float adjDf = dot4(adjC, cache.dv);
+    if constexpr (TFACC == kTfAccSmem) {
+      const float a[4] = {adjC.x, adjC.y, adjC.z, adjC.w};
+      acc.add_pair(fl, a, df);
+    } else if constexpr (HAS_TF) {
+      const int i0 = min(max(fl, 0), R - 1), i1 = min(max(fl + 1, 0), R - 1);
       const float w0 = 1.f - df;
       const float a0[4] = {adjC.x * w0, adjC.y * w0, adjC.z * w0, adjC.w * w0};
       const float a1[4] = {adjC.x * df, adjC.y * df, adjC.z * df, adjC.w * df};
@@ -196,31 +235,44 @@ DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC
     }
     return adjDf * float(R);
   } else if constexpr (TF == kTfLinear) {  // :315-400
-    const int i = linear_interval(s_tf, R, density);
-    const f4 v0 = lds4(s_tf + 8 * i), v1 = lds4(s_tf + 8 * (i + 1));
-    const float p0 = s_tf[8 * i + 4], p1 = s_tf[8 * (i + 1) + 4];
-    const float d2 = fmaxf(p0, fminf(density, p1));
-    const float frac = (d2 - p0) / (p1 - p0);
-    const float adjFrac = dot4(adjC, f4{v1.x - v0.x, v1.y - v0.y, v1.z - v0.z, v1.w - v0.w});
+    const int i = cache.i;
+    const float p0 = cache.p0, p1 = cache.p1, d2 = cache.d2;
+    const float rcp = cache.rcp;                                 // 1 / (p1 - p0), staged per row
+    const float frac = cache.frac;                               // the IEEE quotient (d2 - p0) / (p1 - p0)
+    const float adjFrac = dot4(adjC, cache.dv);
+    const float adjD = div_rcp(adjFrac, p1 - p0, rcp);           // adjFrac / (p1 - p0)
     if constexpr (HAS_TF) {
-      const float denom = (p1 - p0) * (p1 - p0);
-      const float w0 = 1.f - frac;
-      const float a0[5] = {adjC.x * w0, adjC.y * w0, adjC.z * w0, adjC.w * w0, adjFrac * (d2 - p1) / denom};
-      const float a1[5] = {adjC.x * frac, adjC.y * frac, adjC.z * frac, adjC.w * frac, adjFrac * (p0 - d2) / denom};
-      acc.add_row(i, a0);
-      acc.add_row(i + 1, a1);
+      // adjFrac (d2 - p1) / (p1 - p0)^2 and adjFrac (p0 - d2) / (p1 - p0)^2 (:377-384) as two exact quotients by
+      // (p1 - p0): the value of the reference's single division up to one rounding
+      const float g0 = div_rcp(adjD * (d2 - p1), p1 - p0, rcp), g1 = div_rcp(adjD * (p0 - d2), p1 - p0, rcp);
+      if constexpr (TFACC == kTfAccSmem) {
+        const float a[4] = {adjC.x, adjC.y, adjC.z, adjC.w};
+        acc.add_pair(i, a, frac);
+        acc.row[0][4] += g0;
+        acc.row[1][4] += g1;
+      } else {
+        const float w0 = 1.f - frac;
+        const float a0[5] = {adjC.x * w0, adjC.y * w0, adjC.z * w0, adjC.w * w0, g0};
+        const float a1[5] = {adjC.x * frac, adjC.y * frac, adjC.z * frac, adjC.w * frac, g1};
+        acc.add_row(i, a0);
+        acc.add_row(i + 1, a1);
+      }
     }
-    return adjFrac / (p1 - p0);  // passes through the clamp unconditionally ("#if 1", :350-352)
+    return adjD;  // passes through the clamp unconditionally ("#if 1", :350-352)
   } else if constexpr (TF == kTfGaussian) {  // :562-614
     float adjDensity = 0.f;
     auto body = [&](int i, float* g, float ni) {
       const f4 ci = lds4(s_tf + 8 * i);
       const float mu = s_tf[8 * i + 4], sigma = s_tf[8 * i + 5];
-      const float f1 = div_rcp(mu - density, sigma * sigma, s_tf[8 * i + 7]) * ni;
+      const float f1 = gauss_slope(density, s_tf + 8 * i) * ni;
       const float dc = dot4(adjC, ci);
       adjDensity = fmaf(dc, f1, adjDensity);
       if constexpr (HAS_TF) {
+#if DVR_FAST_GAUSS_ARG
+        const float f2 = (f1 * (mu - density)) * (sigma * s_tf[8 * i + 7]);  // 1 / sigma = sigma / sigma^2
+#else
         const float f2 = f1 * (mu - density) / sigma;
+#endif
         g[0] = adjC.x * ni; g[1] = adjC.y * ni; g[2] = adjC.z * ni; g[3] = adjC.w * ni;
         g[4] = -dc * f1;
         g[5] = dc * f2;
@@ -231,7 +283,7 @@ DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC
       for (int i = 0; i < kRegRows; ++i)
         if (i < R) {
           float g[6];
-          body(i, g, cache[i]);
+          body(i, g, cache.ni[i]);
 #pragma unroll
           for (int c = 0; c < 6; ++c) acc.g[i * 6 + c] += g[c];
         }
@@ -240,12 +292,12 @@ DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC
       for (int i = 0; i < kRegRows; ++i)
         if (i < R) {
           float g[6];
-          body(i, g, cache[i]);
+          body(i, g, cache.ni[i]);
           if constexpr (HAS_TF) acc.add_row(i, g);
         }
       for (int i = kRegRows; i < R; ++i) {
         float g[6];
-        body(i, g, gauss_exp(gauss_arg(density, s_tf + 8 * i)));
+        body(i, g, gauss_exp(gauss_arg<false>(density, s_tf + 8 * i)));
         if constexpr (HAS_TF) acc.add_row(i, g);
       }
     }
@@ -298,10 +350,37 @@ DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC
   }
 }
 
-template <int FILTER, int TF, int BLEND, bool HAS_VOL, int TFACC, bool HAS_RAY>
-// HAS_RAY instances: <= 80 registers for 6 CTAs/SM (C3 adjoint(camera) 26.2 -> 24.8 ms). Forcing more CTAs on the
-// others (forward <= 40 registers, adjoint(volume) <= 48) was measured and is slower: they are issue bound.
-__global__ void __launch_bounds__(kThreads, HAS_RAY ? 6 : 1) k_adjoint(const RayInputs in, const AdjointArgs aa) {
+// Which per-ray gradients the instance carries: none, the stepsize only (one accumulator; C5), or the camera's ray
+// start / direction (+ the stepsize when AdjointArgs::hasStep)
+enum : int { kRayNone = 0, kRayStep = 1, kRayCam = 2 };
+
+// Resident CTAs the register allocation aims for. Instances that differentiate the ray: 6 CTAs/SM (<= 80 registers;
+// C3 adjoint(camera) 26.2 -> 24.8 ms). The full-flag instance of C5 (volume + TF + stepsize) is latency-sensitive
+// rather than purely issue-bound (issue slots 70 % busy, profiles/r02_ncu_kernels.md): measured at 4 CTAs / 108
+// registers 39.1 ms, 5 CTAs / 96 registers 33.0 ms, 6 CTAs / 80 registers 30.9 ms (with 8 bytes of stack; the first
+// version of this instance spilled 32 bytes under the same cap and took 36.3 ms -- the TF cache, the stepsize-only
+// ray mode and the factored blend adjoint removed the pressure). Register accumulators of a Gaussian table and the
+// GaussianLog adjoint need 4 CTAs (<= 128 registers) to stay out of local memory. Forcing more CTAs on the instances
+// without ray gradients (forward <= 40 registers, adjoint(volume) <= 48) was measured and is slower.
+#ifndef DVR_ADJ_CTAS_2
+#define DVR_ADJ_CTAS_2 6   // ray gradients + volume + TF state: <= 80 registers (8 bytes of stack in the C5 instance)
+#endif
+#ifndef DVR_ADJ_CTAS_1
+#define DVR_ADJ_CTAS_1 6   // ray gradients + one of the two: <= 80 registers
+#endif
+template <int TF, bool HAS_VOL, int TFACC, int RAY>
+constexpr int adjoint_min_ctas() {
+  if (RAY == kRayNone) return 1;
+  // register accumulators of a Gaussian table (up to kRegRows x 6 floats of state): <= 128 registers
+  if ((TFACC == kTfAccReg && TF == kTfGaussian) || TF == kTfGaussianLog) return 4;
+  const int extra = (HAS_VOL ? 1 : 0) + (TFACC != kTfAccNone ? 1 : 0);
+  return extra == 2 ? DVR_ADJ_CTAS_2 : (extra == 1 ? DVR_ADJ_CTAS_1 : 6);
+}
+
+template <int FILTER, int TF, int BLEND, bool HAS_VOL, int TFACC, int RAY>
+__global__ void __launch_bounds__(kThreads, adjoint_min_ctas<TF, HAS_VOL, TFACC, RAY>()) k_adjoint(const RayInputs in,
+                                                                                             const AdjointArgs aa) {
+  constexpr bool HAS_RAY = RAY != kRayNone;
   extern __shared__ __align__(16) float smem[];
   constexpr int ROW = TfLayout<TF>::kRow;
   constexpr int CH = TfChannels<TF>::v;
@@ -320,7 +399,7 @@ __global__ void __launch_bounds__(kThreads, HAS_RAY ? 6 : 1) k_adjoint(const Ray
   thread_pixel(x, y);
   const bool active = x < in.W && y < in.H;
   TfGrad<TF, TFACC> tfg;
-  tfg.init(TFACC == kTfAccSmem ? s_acc + warp * entries : s_acc);
+  tfg.init(TFACC == kTfAccSmem ? s_acc + warp * entries : s_acc, in.R);
 
   if (active) {
     const Ray ray = make_ray(in, x, y, b);
@@ -374,14 +453,18 @@ __global__ void __launch_bounds__(kThreads, HAS_RAY ? 6 : 1) k_adjoint(const Ray
         }
         adjDensity = (density > 0.f && density < 1.f) ? adjDc : 0.f;
       } else {
-        float tfCache[kRegRows];
+        TfCache<TF> tfCache;
         const f4 cur = tf_eval_cached<TF>(s_tf, in.R, density, tfCache);
         f4 adjCur;
-        blend_adjoint<BLEND>(acc, adjAcc, cur, ray.step, adjCur, adjStepBlend);
+        blend_adjoint<BLEND, false>(acc, adjAcc, cur, ray.step, adjCur, adjStepBlend);
         adjDensity = tf_adjoint<TF, TFACC>(s_tf, in.R, density, adjCur, tfg, tfCache);
       }
       const f3 g = smp.template adjoint<HAS_RAY>(adjDensity);
-      if constexpr (HAS_RAY) {
+      if constexpr (RAY == kRayStep) {
+        // d pos / d stepsize = i dir / voxel = i pd: one dot product and one accumulator
+        adjStep = aa.compatStepOverwrite ? adjStepBlend : adjStep + adjStepBlend;
+        adjStep = fmaf(fmaf(g.z, ray.pd.z, fmaf(g.y, ray.pd.y, g.x * ray.pd.x)), fi, adjStep);
+      } else if constexpr (RAY == kRayCam) {
         // the reference overwrites its accumulator with the blend term (see compat flag)
         adjStep = aa.compatStepOverwrite ? adjStepBlend : adjStep + adjStepBlend;
         const f3 w = {g.x * ray.invVoxel.x, g.y * ray.invVoxel.y, g.z * ray.invVoxel.z};
@@ -398,7 +481,7 @@ __global__ void __launch_bounds__(kThreads, HAS_RAY ? 6 : 1) k_adjoint(const Ray
         if (aa.stepAtomic) atomicAdd(p, adjStep);
         else *p = adjStep;
       }
-      if (aa.hasCam) {
+      if (RAY == kRayCam && aa.hasCam) {
         float* ps = aa.adjRayStart + b * aa.rsB + y * aa.rsY + x * aa.rsX;
         float* pd = aa.adjRayDir + b * aa.rdB + y * aa.rdY + x * aa.rdX;
         if (aa.camAtomic) {

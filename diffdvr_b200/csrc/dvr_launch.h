@@ -24,11 +24,14 @@ cudaError_t launch_forward(int filter, int tf, int blend, const RayInputs& in, c
                            dim3 grid, size_t smem, cudaStream_t stream);
 
 // tfacc: 0 none, 1 register accumulators, 2 shared-memory tables (see dvr_kernels.cuh)
-cudaError_t launch_adjoint(int filter, int tf, int blend, bool hasVol, int tfacc, bool hasRay,
+// ray: 0 no per-ray gradients, 1 stepsize only, 2 camera (+ stepsize)
+cudaError_t launch_adjoint(int filter, int tf, int blend, bool hasVol, int tfacc, int ray,
                            const RayInputs& in, const AdjointArgs& aa, dim3 grid, size_t smem,
                            cudaStream_t stream);
 
-// chunk: number of tangent slots per pass (1, 6 or 8); 0 = the input-major single pass (ray / stepsize tangents only)
+// chunk: number of tangent slots per pass (1, 6 or 8); 0 = the input-major single pass (ray / stepsize tangents only);
+// -1 = the sample-major single pass for TF tangents (Identity / Texture / Linear; reads `out` as written by the plain
+// forward kernel and accumulates into ga.grad)
 cudaError_t launch_forward_gradients(int filter, int tf, int blend, int chunk, bool hasPos, bool hasTf,
                                      const RayInputs& in, const ForwardOutputs& out,
                                      const ForwardGradArgs& ga, dim3 grid, size_t smem,
@@ -41,6 +44,8 @@ cudaError_t launch_adjoint_preshaded(int blend, bool hasVol, bool hasRay, const 
                                      const AdjointArgs& aa, dim3 grid, cudaStream_t stream);
 
 cudaError_t launch_fwdvars_to_gradients(const FwdVarsArgs& a, cudaStream_t stream);
+// zero-fill of a strided B*H*W*D*4 Jacobian (dvr_misc.cu)
+cudaError_t launch_zero_jacobian(const ForwardGradArgs& ga, int W, int H, int B, cudaStream_t stream);
 
 cudaError_t launch_count_cells(const RayInputs& in, const int* term, long long tB, long long tY, long long tX,
                                unsigned long long* counts, dim3 grid, cudaStream_t stream);
@@ -66,7 +71,7 @@ cudaError_t launch_downsample_volume(const DownsampleArgs& a, cudaStream_t strea
 
 // per-(tf, blend) translation units (parallel compilation)
 #define DVR_DECL_ADJ(TF, BL)                                                                          \
-  cudaError_t launch_adjoint_##TF##_##BL(int filter, bool hasVol, int tfacc, bool hasRay,             \
+  cudaError_t launch_adjoint_##TF##_##BL(int filter, bool hasVol, int tfacc, int ray,                 \
                                          const RayInputs& in, const AdjointArgs& aa, dim3 grid,       \
                                          size_t smem, cudaStream_t stream);
 DVR_FOR_EACH_ADJOINT_INSTANCE(DVR_DECL_ADJ)

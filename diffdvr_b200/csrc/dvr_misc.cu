@@ -159,6 +159,25 @@ cudaError_t launch_count_cells(const RayInputs& in, const int* term, long long t
   return launch_kernel(k_count_cells, grid, kThreads, 0, s, in, term, tB, tY, tX, counts);
 }
 
+// zero-fill of a strided B*H*W*D*4 Jacobian (dense ones take cudaMemsetAsync)
+__global__ void k_zero_jacobian(const ForwardGradArgs ga, int W, int H, int B) {
+  const long long total = (long long)B * H * W * ga.D * 4;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    long long r = i;
+    const int c = int(r & 3); r >>= 2;
+    const int d = int(r % ga.D); r /= ga.D;
+    const int x = int(r % W); r /= W;
+    const int y = int(r % H); r /= H;
+    ga.grad[r * ga.gB + y * ga.gY + x * ga.gX + d * ga.gD + c * ga.gC] = 0.f;
+  }
+}
+
+cudaError_t launch_zero_jacobian(const ForwardGradArgs& ga, int W, int H, int B, cudaStream_t s) {
+  const long long total = (long long)B * H * W * ga.D * 4;
+  const unsigned blocks = unsigned(total / 256 + 1 < 148 * 16 ? total / 256 + 1 : 148 * 16);
+  return launch_kernel(k_zero_jacobian, dim3(blocks), 256, 0, s, ga, W, H, B);
+}
+
 cudaError_t launch_fwdvars_to_gradients(const FwdVarsArgs& a, cudaStream_t s) {
   const long long pixels = (long long)a.W * a.H;
   const dim3 grid((unsigned)((pixels + 255) / 256), 1, a.B);

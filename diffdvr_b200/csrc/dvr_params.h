@@ -104,6 +104,10 @@ struct ForwardGradArgs {
   long long dtB, dtR, dtC;
   float* grad;                       // B*H*W*D*4
   long long gB, gY, gX, gD, gC;
+  int exactPos;                      // k_tf_jacobian: sample positions in the reference's operation order (when the
+                                     // colour it reads was written by k_forward_gradients_inputs)
+  int gradVec4;                      // 1: gC == 1, every other stride a multiple of 4, 16-byte aligned base -> the four
+                                     // channels of a slot are one 16-byte access
 };
 
 struct FwdVarsArgs {

@@ -27,7 +27,7 @@ __global__ void __launch_bounds__(256) k_preshade(const RayInputs in, const Pres
       c[0] = v.x; c[a.cC] = v.y; c[2 * a.cC] = v.z; c[3 * a.cC] = v.w;
     } else {
       const f4 adjC = {__ldg(c), __ldg(c + a.cC), __ldg(c + 2 * a.cC), __ldg(c + 3 * a.cC)};
-      float cache[kRegRows];
+      TfCache<TF> cache;
       tf_eval_cached<TF>(s_tf, in.R, density, cache);
       TfGrad<TF, kTfAccNone> none;
       a.adjVolume[(long long)x * a.ax + (long long)y * a.ay + (long long)z * a.az] =

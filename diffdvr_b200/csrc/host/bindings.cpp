@@ -55,6 +55,11 @@ class GPUTimer {
 }  // namespace
 
 PYBIND11_MODULE(pyrenderer, m) {
+  // the structs this module passes by pointer are those of the header it was compiled against
+  if (dvr_abi_version() != DVR_ABI_VERSION)
+    throw std::runtime_error("pyrenderer was built against ABI version " + std::to_string(DVR_ABI_VERSION) +
+                             " of libdvr_b200.so, the loaded library has version " + std::to_string(dvr_abi_version()) +
+                             ": rebuild (diffdvr_b200/csrc/host/build_pyrenderer.py)");
   Renderer::initCuda();
   m.doc() = "python bindings for the differentiable volume renderer (B200-native build)";
 

@@ -113,9 +113,9 @@ def get(name: str, **override) -> Workload:
         "C1": dict(description="forward render of ML(128) at 256^2, trilinear, piecewise-linear TF, BeerLambert, "
                                "ReferenceFrame camera, step 0.5 voxel",
                    vol_kind="ml", n=128, res=256, views=1, batch=1, tf_kind="linear", step_voxels=0.5, camera="frame"),
-        "C2": dict(description="TF reconstruction: SKULL(256), 8 views @256^2 in launches of 4, Texture TF R=64, "
+        "C2": dict(description="TF reconstruction: SKULL(256), 8 views @256^2 in one launch, Texture TF R=64, "
                                "step 0.2 voxel, forward + L1 loss + adjoint(hasTF, delayed flag)",
-                   vol_kind="skull", n=256, res=256, views=8, batch=4, tf_kind="texture", step_voxels=0.2,
+                   vol_kind="skull", n=256, res=256, views=8, batch=8, tf_kind="texture", step_voxels=0.2,
                    camera="frame", adjoint=("tf",), delayed_tf=True),
         "C3": dict(description="best viewpoint: SKULL(256), 8 views @512^2, per-pixel rays, Gaussian TF R=4, step 0.2 "
                                "voxel, forward-mode D=6 (ray start / direction) + forward_variables_to_gradients",

@@ -290,9 +290,15 @@ typedef struct DvrCallOptions {
   int64_t max_scratch_bytes;         /* cap on the per-call / workspace QUAD buffers of this call; above it the call
                                         takes the in-place path (counted, see dvr_get_stat). <= 0: 16 GiB */
   DvrWorkspace* workspace;           /* may be NULL */
+  int32_t forward_mode_tf;           /* forward-mode with TF tangents: 0 automatic (Identity / Texture / Linear tables:
+                                        ONE sample-major marching pass for any D, csrc/dvr_tfjac.cuh; Gaussian:
+                                        ceil(D / 8) slot-major passes), 1 always the slot-major passes (the reference's
+                                        scheme in chunks; kept for A/B measurements). Read only when struct_size
+                                        covers it (a 32-byte DvrCallOptions of ABI 2.0 stays valid) */
+  int32_t reserved0;
 } DvrCallOptions;
 
-DVR_API void dvr_call_options_init(DvrCallOptions* options); /* the defaults: -1, 0, 0, 0, NULL */
+DVR_API void dvr_call_options_init(DvrCallOptions* options); /* the defaults: -1, 0, 0, 0, NULL, 0 */
 
 DVR_API DvrWorkspace* dvr_workspace_create(void);            /* on the current device; NULL on failure */
 DVR_API void dvr_workspace_destroy(DvrWorkspace* ws);        /* frees its device buffers (synchronises) */
@@ -362,7 +368,7 @@ DVR_API const char* dvr_last_error(void);
 
 /* ABI version of this header. */
 DVR_API int32_t dvr_abi_version(void);
-#define DVR_ABI_VERSION 2
+#define DVR_ABI_VERSION 3 /* 3: DvrCallOptions grew (forward_mode_tf); dvr_call_options_init writes sizeof(DvrCallOptions) of THIS header */
 
 #ifdef __cplusplus
 }

@@ -77,8 +77,8 @@ __global__ void k_tf_adjoint(const RayInputs in, int n, const float* density, co
   constexpr int CH = TfChannels<TF>::v;
   float* table = adjTf + (long long)i * in.R * CH;
   TfGrad<TF, TFACC> tfg;
-  tfg.init(table);
-  float cache[kRegRows];
+  tfg.init(table, in.R);
+  TfCache<TF> cache;
   tf_eval_cached<TF>(s_tf, in.R, density[i], cache);
   const f4 adjC = {g[4 * i], g[4 * i + 1], g[4 * i + 2], g[4 * i + 3]};
   adjDensity[i] = tf_adjoint<TF, TFACC>(s_tf, in.R, density[i], adjC, tfg, cache);

@@ -34,7 +34,7 @@ def test_library_loads_without_gpu_and_exports_every_declared_symbol():
     lib = capi.load()   # raises if the .so is missing: there is no fallback
     for s in declared_symbols():
         assert hasattr(lib.lib, s), f"{s} declared in include/dvr_b200.h but not exported"
-    assert lib.lib.dvr_abi_version() == 2
+    assert lib.lib.dvr_abi_version() == 3
     # nothing else with default visibility leaks out of the library
     out = subprocess.run(["nm", "-D", "--defined-only", capi.library_path()], capture_output=True, text=True).stdout
     exported = {l.split()[-1] for l in out.splitlines() if " T " in l}

@@ -93,6 +93,47 @@ def run(name, reps, flush, adjoint_override=None):
     return out
 
 
+def run_fwdmode_tf(reps, flush):
+    """Forward-mode with TF tangents: one view of the C2 scene (SKULL(256), 256^2, Texture R=64 ->
+    D = 256) and a D = 32 table (Texture R=8, the reference's testConsistencyTF.cpp shape), the one-pass sample-major
+    kernel against the slot-major ceil(D/8) passes it replaces."""
+    dev = torch.device("cuda", 0)
+    lib = capi.load()
+    rows = []
+    for label, R in (("C2 scene, Texture R=64 (D=256)", 64), ("C2 scene, Texture R=8 (D=32)", 8)):
+        w = workloads.get("C2", views=1, batch=1)
+        tf = torch.from_numpy(np.ascontiguousarray(
+            workloads.synthetic.tf_texture_from_linear(workloads.synthetic.tf_linear_two_peaks(), R))).to(dev)
+        inp = w.inputs(lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev), views=[0], tf=tf)
+        ws = lib.workspace()
+        ws.set_volume(inp.volume)
+        D = R * 4
+        d_tf = torch.arange(D, dtype=torch.int32, device=dev).reshape(1, R, 4)
+        st = capi.make_fd_settings(D, d_tf=d_tf, has_tf_derivatives=True)
+        color = torch.empty(1, w.res, w.res, 4, device=dev)
+        term = torch.empty(1, w.res, w.res, dtype=torch.int32, device=dev)
+        grad = torch.empty(1, w.res, w.res, D, 4, device=dev)
+        out = {"case": label, "D": D, "jacobian_mib": grad.numel() * 4 / 2**20}
+        res = {}
+        for name, mode in (("one_pass", 0), ("slot_major", 1)):
+            opts = capi.make_call_options(workspace=ws, forward_mode_tf=mode)
+            n0 = lib.launch_count()
+            lib.render_forward_gradients(inp, st, color, term, grad, options=opts)
+            torch.cuda.synchronize()
+            out[name + "_launches"] = lib.launch_count() - n0
+            out[name + "_ms"] = timed(lambda: lib.render_forward_gradients(inp, st, color, term, grad, options=opts),
+                                      reps, flush)
+            res[name] = grad.clone()
+        out["speedup"] = out["slot_major_ms"] / out["one_pass_ms"]
+        out["rel_l2_between_them"] = float((res["one_pass"] - res["slot_major"]).norm() / res["slot_major"].norm())
+        ws.close()
+        del res
+        torch.cuda.empty_cache()
+        rows.append(out)
+        print(json.dumps(out), flush=True)
+    return rows
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--configs", default="C1,C2,C3,C4,C5")
@@ -100,12 +141,16 @@ def main():
     ap.add_argument("--out", default=None)
     ap.add_argument("--profile", action="store_true",
                     help="launch every kernel exactly once (no warm-up, one repetition): the run to put under ncu")
+    ap.add_argument("--fwdmode-tf", action="store_true", help="forward-mode TF tangents: one pass vs slot-major passes")
     a = ap.parse_args()
     if a.profile:
         global WARMUP
         WARMUP, a.reps = 0, 1
     assert torch.cuda.is_available(), "needs a CUDA device (no CPU fallback)"
     flush = torch.empty(256 * 1024 * 1024 // 4, device="cuda")
+    if a.fwdmode_tf:
+        run_fwdmode_tf(a.reps, flush)
+        return
     rows = []
     for name in a.configs.split(","):
         r = run(name, a.reps, flush)
