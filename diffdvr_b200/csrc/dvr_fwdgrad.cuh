@@ -297,6 +297,10 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
     if (acc.w > in.earlyOut) break;
     const f3 p = sample_pos<true>(ray, t);
     const float density = smp.fetch(in, nullptr, p.x, p.y, p.z);
+    if constexpr (DVR_PREFETCH_RAY) {
+      const f3 pn = sample_pos<false>(ray, sample_t(ray, fi + 1.0f));
+      smp.prefetch_cell(in, pn.x, pn.y, pn.z);
+    }
     // d density / d input
     float dd[NI];
     if constexpr (FILTER == kFilterNearest) {

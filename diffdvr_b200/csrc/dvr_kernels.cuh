@@ -37,6 +37,10 @@ __global__ void __launch_bounds__(kThreads) k_forward(const RayInputs in, const 
       if (acc.w > in.earlyOut) break;
       const f3 p = sample_pos<false>(ray, t);
       const float dc = fmaxf(0.f, fminf(smp.fetch(in, nullptr, p.x, p.y, p.z), 1.f));
+      if constexpr (DVR_PREFETCH_FWD) {
+        const f3 pn = sample_pos<false>(ray, sample_t(ray, fi + 1.0f));
+        smp.prefetch_cell(in, pn.x, pn.y, pn.z);
+      }
       const float alpha = blend_alpha<BLEND>(dc * sa, ray.step);
       const float om = 1.f - acc.w;
       acc.x = fmaf(om * (dc * sc), alpha, acc.x);
@@ -50,6 +54,10 @@ __global__ void __launch_bounds__(kThreads) k_forward(const RayInputs in, const 
       if (acc.w > in.earlyOut) break;
       const f3 p = sample_pos<false>(ray, t);
       const float density = smp.fetch(in, nullptr, p.x, p.y, p.z);
+      if constexpr (DVR_PREFETCH_FWD) {
+        const f3 pn = sample_pos<false>(ray, sample_t(ray, fi + 1.0f));
+        smp.prefetch_cell(in, pn.x, pn.y, pn.z);
+      }
       const f4 cur = tf_eval<TF>(smem, in.R, density);
       acc = blend_over(acc, cur, blend_alpha<BLEND>(cur.w, ray.step));
     }
@@ -437,6 +445,12 @@ __global__ void __launch_bounds__(kThreads, adjoint_min_ctas<TF, HAS_VOL, TFACC,
         p = {xy.x, xy.y, fmaf(fi, dp.z, p0.z)};
       }
       const float density = smp.fetch(in, &aa, p.x, p.y, p.z);
+      if constexpr (HAS_RAY ? DVR_PREFETCH_RAY : DVR_PREFETCH_ADJ) {
+        // the next sample's position in the cheap form (a prefetch may guess wrong next to a cell face)
+        const float fn = fi - 1.0f;
+        const float2 xy = pk_fma(fn, make_float2(dp.x, dp.y), make_float2(p0.x, p0.y));
+        smp.prefetch_cell(in, xy.x, xy.y, fmaf(fn, dp.z, p0.z));
+      }
       float adjDensity, adjStepBlend;
       if constexpr (TF == kTfIdentity) {
         // r = g = b (renderer_tf.cuh:62-104): one colour lane through the blend inversion and the TF adjoint

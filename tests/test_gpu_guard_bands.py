@@ -14,7 +14,7 @@ from diffdvr_b200 import capi
 
 pytestmark = pytest.mark.gpu
 
-SENTINEL = 1234.5
+SENTINEL = 12345.0  # integral: the int32 buffers hold it exactly
 PAD = 64  # elements on both sides
 
 
