@@ -833,8 +833,12 @@ int dvr_render_forward_gradients_ex(const DvrInputs* inputs, const DvrForwardDif
                    "dvr_render_forward_gradients", s);
       return;
     }
-    if (!ctx.fwdTfSlotMajor && (tf == kTfIdentity || tf == kTfTexture || tf == kTfLinear)) {
-      // TF tangents of a two-row (or scalar) table: ONE sample-major pass for any D (dvr_tfjac.cuh). It needs the
+    // Gaussian tables: the one-pass kernel keeps 15 moments per row and thread in shared memory (R <= 28 fits);
+    // larger tables take the slot-major passes
+    const size_t smemGauss = smem + size_t(15) * c.ri.R * kThreads * sizeof(float);
+    const bool gaussOnePass = tf == kTfGaussian && smemGauss <= 200 * 1024;
+    if (!ctx.fwdTfSlotMajor && (tf == kTfIdentity || tf == kTfTexture || tf == kTfLinear || gaussOnePass)) {
+      // TF tangents in ONE sample-major pass for any D (dvr_tfjac.cuh). It needs the
       // final pixel values, so the colour comes first: from the input-major pass when ray / stepsize tangents are
       // traced as well (it writes all D slots, zeros where no input maps), else from the plain forward kernel
       // followed by a zero-fill of the Jacobian.
@@ -859,7 +863,7 @@ int dvr_render_forward_gradients_ex(const DvrInputs* inputs, const DvrForwardDif
       }
       ga.exactPos = hasStep || hasCam;
       after_launch(launch_forward_gradients(filter, tf, inputs->blend_mode, -1, hasStep || hasCam, true, c.ri, fo, ga,
-                                            tile_grid(c), smem, s),
+                                            tile_grid(c), gaussOnePass ? smemGauss : smem, s),
                    "dvr_render_forward_gradients", s);
       return;
     }

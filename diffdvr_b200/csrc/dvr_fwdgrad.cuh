@@ -283,9 +283,13 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
   if (x >= in.W || y >= in.H) return;
 
   const Ray ray = make_ray(in, x, y, b);  // box intersection on VALUES only (:201-208)
-  float ax[NI], ay[NI], az[NI], aw[NI];   // d acc / d input
+  // d acc / d input, the seven inputs as four register pairs (0,1) (2,3) (4,5) (6,-): the per-input tangent update is
+  // the same arithmetic for every input, so it runs on FFMA2 / FMUL2 / FADD2 (half the issue slots; per-lane results
+  // identical to the scalar form)
+  constexpr int NP = 4;
+  float2 ax[NP], ay[NP], az[NP], aw[NP];
 #pragma unroll
-  for (int j = 0; j < NI; ++j) ax[j] = ay[j] = az[j] = aw[j] = 0.f;
+  for (int j = 0; j < NP; ++j) ax[j] = ay[j] = az[j] = aw[j] = make_float2(0.f, 0.f);
   f4 acc = {0.f, 0.f, 0.f, 0.f};
   Sampler<FILTER, false> smp;
   smp.init(in, b, nullptr, 0);
@@ -302,15 +306,17 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
       smp.prefetch_cell(in, pn.x, pn.y, pn.z);
     }
     // d density / d input
-    float dd[NI];
+    float2 dd[NP];
     if constexpr (FILTER == kFilterNearest) {
 #pragma unroll
-      for (int j = 0; j < NI; ++j) dd[j] = 0.f;  // no positional tangent (interpolation.cuh:52-65)
+      for (int j = 0; j < NP; ++j) dd[j] = make_float2(0.f, 0.f);  // no positional tangent (interpolation.cuh:52-65)
     } else {
       const f3 g = smp.template adjoint<true>(1.0f);  // gradient of the trilinear cell at the sample
-      dd[0] = g.x * ray.invVoxel.x; dd[1] = g.y * ray.invVoxel.y; dd[2] = g.z * ray.invVoxel.z;
-      dd[3] = t * dd[0]; dd[4] = t * dd[1]; dd[5] = t * dd[2];
-      dd[6] = fi * fmaf(g.z, ray.pd.z, fmaf(g.y, ray.pd.y, g.x * ray.pd.x));
+      const float d0 = g.x * ray.invVoxel.x, d1 = g.y * ray.invVoxel.y, d2 = g.z * ray.invVoxel.z;
+      dd[0] = make_float2(d0, d1);
+      dd[1] = make_float2(d2, t * d0);
+      dd[2] = pk_mul(t, make_float2(d1, d2));
+      dd[3] = make_float2(fi * fmaf(g.z, ray.pd.z, fmaf(g.y, ray.pd.y, g.x * ray.pd.x)), 0.f);
     }
     // colour cv and its slope cs = d colour / d density
     f4 cv, cs;
@@ -350,17 +356,17 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
     const float oav = om * av;
     const float kx = cs.x * oav, ky = cs.y * oav, kz = cs.z * oav, kw = cs.w * sv;
 #pragma unroll
-    for (int j = 0; j < NI; ++j) {
-      float ws = kw * dd[j];            // (w s)' = w' s + w s', s' = 1 for the stepsize input only
-      if (j == 6) ws += wv;
-      float ad;
-      if constexpr (BLEND == kBlendBeer) ad = e * ws;
-      else ad = active ? ws : 0.f;
-      const float oad = fmaf(-aw[j], av, om * ad);  // d((1 - acc.w) alpha)
-      ax[j] += fmaf(kx, dd[j], cv.x * oad);
-      ay[j] += fmaf(ky, dd[j], cv.y * oad);
-      az[j] += fmaf(kz, dd[j], cv.z * oad);
-      aw[j] += oad;
+    for (int j = 0; j < NP; ++j) {
+      float2 ws = pk_mul(kw, dd[j]);     // (w s)' = w' s + w s', s' = 1 for the stepsize input (pair 3, first half) only
+      if (j == 3) ws.x += wv;
+      float2 ad;
+      if constexpr (BLEND == kBlendBeer) ad = pk_mul(e, ws);
+      else ad = active ? ws : make_float2(0.f, 0.f);
+      const float2 oad = pk_fma(-av, aw[j], pk_mul(om, ad));  // d((1 - acc.w) alpha) = -acc.w' alpha + om alpha'
+      ax[j] = pk_add(ax[j], pk_fma(kx, dd[j], pk_mul(cv.x, oad)));
+      ay[j] = pk_add(ay[j], pk_fma(ky, dd[j], pk_mul(cv.y, oad)));
+      az[j] = pk_add(az[j], pk_fma(kz, dd[j], pk_mul(cv.z, oad)));
+      aw[j] = pk_add(aw[j], oad);
     }
     acc.x = fmaf(om * cv.x, av, acc.x);
     acc.y = fmaf(om * cv.y, av, acc.y);
@@ -376,7 +382,10 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
 #pragma unroll
     for (int j = 0; j < NI; ++j) {
       const int slot = j < 3 ? ga.dRayStart[j] : (j < 6 ? ga.dRayDir[j - 3] : ga.dStep);
-      if (slot == d) { gx += ax[j]; gy += ay[j]; gz += az[j]; gw += aw[j]; }
+      if (slot == d) {
+        gx += (j & 1) ? ax[j >> 1].y : ax[j >> 1].x; gy += (j & 1) ? ay[j >> 1].y : ay[j >> 1].x;
+        gz += (j & 1) ? az[j >> 1].y : az[j >> 1].x; gw += (j & 1) ? aw[j >> 1].y : aw[j >> 1].x;
+      }
     }
     store4(g + d * ga.gD, ga.gC, ga.gradVec4, gx, gy, gz, gw);
   }

@@ -25,8 +25,8 @@ template <int F>
 static cudaError_t by_chunk(int n, bool p, bool t, const RayInputs& in, const ForwardOutputs& out,
                             const ForwardGradArgs& ga, dim3 g, size_t sm, cudaStream_t s) {
   switch (n) {
-    case -1:  // sample-major single pass: TF tangents of Identity / Texture / Linear tables (k_tf_jacobian)
-      if constexpr (DVR_TF == kTfIdentity || DVR_TF == kTfTexture || DVR_TF == kTfLinear) {
+    case -1:  // sample-major single pass: TF tangents (k_tf_jacobian)
+      if constexpr (DVR_TF == kTfIdentity || DVR_TF == kTfTexture || DVR_TF == kTfLinear || DVR_TF == kTfGaussian) {
         if (!t) return kErrNoInstance;
         return launch_kernel(k_tf_jacobian<F, DVR_TF, DVR_BL>, g, kThreads, sm, s, in, out, ga);
       } else {

@@ -191,9 +191,11 @@ DVR_DEV f4 tf_eval_cached(const float* s_tf, int R, float density, TfCache<TF>& 
     int i0, i1;
     texture_coords(density, R, i0, i1, cache.df, cache.fl);
     const f4 v0 = lds4(s_tf + 4 * i0), v1 = lds4(s_tf + 4 * i1);
-    cache.dv = {v1.x - v0.x, v1.y - v0.y, v1.z - v0.z, v1.w - v0.w};
-    const float df = cache.df;
-    return {fmaf(df, cache.dv.x, v0.x), fmaf(df, cache.dv.y, v0.y), fmaf(df, cache.dv.z, v0.z), fmaf(df, cache.dv.w, v0.w)};
+    const float2 dlo = pk_sub(make_float2(v1.x, v1.y), make_float2(v0.x, v0.y));
+    const float2 dhi = pk_sub(make_float2(v1.z, v1.w), make_float2(v0.z, v0.w));
+    cache.dv = {dlo.x, dlo.y, dhi.x, dhi.y};
+    const float2 lo = pk_fma(cache.df, dlo, make_float2(v0.x, v0.y)), hi = pk_fma(cache.df, dhi, make_float2(v0.z, v0.w));
+    return {lo.x, lo.y, hi.x, hi.y};
   } else if constexpr (TF == kTfLinear) {
     const int i = linear_interval(s_tf, R, density);
     const f4 v0 = lds4(s_tf + 8 * i), v1 = lds4(s_tf + 8 * (i + 1));
@@ -415,7 +417,12 @@ __global__ void __launch_bounds__(kThreads, adjoint_min_ctas<TF, HAS_VOL, TFACC,
     const float* ap = aa.adjColor.p + b * aa.adjColor.b + y * aa.adjColor.y + x * aa.adjColor.x;
     f4 acc = {__ldg(cp), __ldg(cp + aa.color.c), __ldg(cp + 2 * aa.color.c), __ldg(cp + 3 * aa.color.c)};
     f4 adjAcc = {__ldg(ap), __ldg(ap + aa.adjColor.c), __ldg(ap + 2 * aa.adjColor.c), __ldg(ap + 3 * aa.adjColor.c)};
-    const int n = __ldg(aa.term + b * aa.tB + y * aa.tY + x * aa.tX);
+    int n = __ldg(aa.term + b * aa.tB + y * aa.tY + x * aa.tX);
+    // A ray whose adjoint colour is zero in all four channels contributes exact zeros to every output (converged or
+    // masked pixels of a reconstruction): skip its march. The per-ray outputs below are still written (as zeros).
+    if (((__float_as_uint(adjAcc.x) | __float_as_uint(adjAcc.y) | __float_as_uint(adjAcc.z) | __float_as_uint(adjAcc.w)) &
+         0x7fffffffu) == 0u)
+      n = 0;
     float adjStep = 0.f;
     f3 adjStart = {0.f, 0.f, 0.f}, adjDir = {0.f, 0.f, 0.f};
     Sampler<FILTER, HAS_VOL> smp;

@@ -17,27 +17,37 @@
 //
 // The output must hold zeros (TF tangents only: the host zero-fills it) or the ray / stepsize tangents written by
 // k_forward_gradients_inputs (slots shared between a TF entry and a ray input add, as unit seeds in one slot do).
-// Gaussian tables touch every row at every sample (no sparsity to exploit; D = 6 R is small): they stay on the
-// slot-major kernel.
+// Gaussian tables touch every row at every sample: nothing sparse, but the same per-sample sensitivities hold, and the
+// per-row parameter tangents reduce to three moments of the row's kernel n_r(d) -- sum w n, sum w n u, sum w n u (d - mu) / sigma
+// with u = (d - mu) / sigma^2 -- for five weights w (T alpha for the colour path, (d alpha / d absorption) G[0..3] for the
+// alpha path): 15 accumulators per row, kept in a per-thread column of shared memory ([entry][thread]: conflict free).
+// One pass for any R that fits (15 R floats per thread: R <= 28); the colour constants c_r are applied once at the end.
 #pragma once
 #include "dvr_device.cuh"
+#include "dvr_kernels.cuh"  // TfCache / tf_eval_cached
 
 namespace dvr {
 
 template <int TF> struct JacRow { static constexpr int n = 5; };          // (colour weight, d/d absorption x 4)
 template <> struct JacRow<kTfLinear> { static constexpr int n = 9; };     // + d/d position x 4
+template <> struct JacRow<kTfGaussian> { static constexpr int n = 1; };   // (unused: the moments live in shared memory)
+constexpr int kGaussMoments = 15;  // per row: 3 moments x (colour weight + 4 alpha-path weights)
 
 template <int FILTER, int TF, int BLEND>
 __global__ void __launch_bounds__(kThreads, 4) k_tf_jacobian(const RayInputs in, const ForwardOutputs fwd,
                                                               const ForwardGradArgs ga) {
-  static_assert(TF == kTfIdentity || TF == kTfTexture || TF == kTfLinear, "two-row / scalar tables only");
+  static_assert(TF == kTfIdentity || TF == kTfTexture || TF == kTfLinear || TF == kTfGaussian, "no GaussianLog");
   extern __shared__ __align__(16) float smem[];
   constexpr int ROW = TfLayout<TF>::kRow;
   constexpr int NR = JacRow<TF>::n;
   const int b = blockIdx.z;
   float* s_tf = smem;
   int* s_dtf = reinterpret_cast<int*>(smem + ((in.R * ROW + 3) & ~3));
+  // Gaussian: this thread's column of the moment table, tab[e * kThreads] for e in [0, 15 R)
+  [[maybe_unused]] float* tab = smem + 2 * ((in.R * ROW + 3) & ~3) + threadIdx.x;
   stage_tf<TF>(in, b, s_tf);
+  if constexpr (TF == kTfGaussian)
+    for (int e = 0; e < kGaussMoments * in.R; ++e) tab[e * kThreads] = 0.f;
   {
     const int* src = ga.dTf + b * ga.dtB;
     for (int i = threadIdx.x; i < in.R * ROW; i += blockDim.x) {
@@ -111,7 +121,10 @@ __global__ void __launch_bounds__(kThreads, 4) k_tf_jacobian(const RayInputs in,
     // the positions of the kernel that wrote `fwd` (uniform branch), so that the accumulator ends at `fin`
     const f3 p = ga.exactPos ? sample_pos<true>(ray, t) : sample_pos<false>(ray, t);
     const float density = smp.fetch(in, nullptr, p.x, p.y, p.z);
-    const f4 cur = tf_eval<TF>(s_tf, in.R, density);
+    [[maybe_unused]] TfCache<TF> tfc;
+    f4 cur;
+    if constexpr (TF == kTfGaussian) cur = tf_eval_cached<TF>(s_tf, in.R, density, tfc);  // the values of tf_eval
+    else cur = tf_eval<TF>(s_tf, in.R, density);
     // blend: the values of blend_alpha / blend_over (the plain forward kernel), plus d alpha / d absorption
     const float xs = cur.w * ray.step;
     float alpha, da;
@@ -135,7 +148,27 @@ __global__ void __launch_bounds__(kThreads, 4) k_tf_jacobian(const RayInputs in,
     }
     const float G[4] = {fmaf(T, cur.x, -(fin.x - acc.x) * inv), fmaf(T, cur.y, -(fin.y - acc.y) * inv),
                         fmaf(T, cur.z, -(fin.z - acc.z) * inv), T - (fin.w - acc.w) * inv};
-    if constexpr (TF == kTfIdentity) {
+    if constexpr (TF == kTfGaussian) {
+      const float wG[4] = {da * G[0], da * G[1], da * G[2], da * G[3]};
+      auto one_row = [&](int r, float nr) {
+        const float* rw = s_tf + 8 * r;
+        const float diff = density - rw[4];
+        const float m1 = nr * (diff * rw[7]);               // d n / d mu    = n (d - mu) / sigma^2
+        const float m2 = m1 * diff * (rw[5] * rw[7]);        // d n / d sigma = n (d - mu)^2 / sigma^3
+        float* t = tab + r * kGaussMoments * kThreads;
+        const float m[3] = {nr, m1, m2};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          t[(5 * k) * kThreads] = fmaf(q, m[k], t[(5 * k) * kThreads]);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) t[(5 * k + 1 + c) * kThreads] = fmaf(wG[c], m[k], t[(5 * k + 1 + c) * kThreads]);
+        }
+      };
+#pragma unroll
+      for (int r = 0; r < kRegRows; ++r)
+        if (r < in.R) one_row(r, tfc.ni[r]);
+      for (int r = kRegRows; r < in.R; ++r) one_row(r, gauss_exp(gauss_arg<false>(density, s_tf + 8 * r)));
+    } else if constexpr (TF == kTfIdentity) {
       // cur = dc (sc, sc, sc, sa): row[0] = (d/d sc [one value for the three colour outputs], d/d sa x 4)
       const float dc = fmaxf(0.f, fminf(density, 1.f));
       row[0][0] = fmaf(q, dc, row[0][0]);
@@ -189,7 +222,22 @@ __global__ void __launch_bounds__(kThreads, 4) k_tf_jacobian(const RayInputs in,
       }
     }
   }
-  if constexpr (TF == kTfIdentity) {
+  if constexpr (TF == kTfGaussian) {
+    for (int r = 0; r < in.R; ++r) {
+      const float* t = tab + r * kGaussMoments * kThreads;
+      const f4 cr = lds4(s_tf + 8 * r);
+      add_colour(r, t[0]);                                   // (r, 0..2): d C[c] / d c_r[c] = sum T alpha n_r
+      const float a[4] = {t[1 * kThreads], t[2 * kThreads], t[3 * kThreads], t[4 * kThreads]};
+      add4(s_dtf[r * ROW + 3], a);                           // (r, 3): absorption
+#pragma unroll
+      for (int k = 1; k < 3; ++k) {                          // (r, 4) mu and (r, 5) sigma: through all four channels
+        const float w0 = t[(5 * k) * kThreads];
+        const float v[4] = {fmaf(cr.x, w0, cr.w * t[(5 * k + 1) * kThreads]), fmaf(cr.y, w0, cr.w * t[(5 * k + 2) * kThreads]),
+                            fmaf(cr.z, w0, cr.w * t[(5 * k + 3) * kThreads]), cr.w * t[(5 * k + 4) * kThreads]};
+        add4(s_dtf[r * ROW + 3 + k], v);
+      }
+    }
+  } else if constexpr (TF == kTfIdentity) {
     // table = (scaleAbsorption, scaleColor): entry (0, 1) moves the three colour outputs alike
     const int sColour = s_dtf[1];
     if (sColour >= 0) {

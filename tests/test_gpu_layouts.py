@@ -71,10 +71,8 @@ def test_forward_mode_quad_copy_equals_in_place_sampling(name):
         launches = lib.launch_count() - n0
         if st.get("d_tf") is None:
             passes = 1                                  # ray / stepsize tangents: the input-major pass
-        elif sc.tf_mode in (capi.TF_IDENTITY, capi.TF_TEXTURE, capi.TF_LINEAR):
-            passes = 2                                  # colour (plain forward or input-major) + the sample-major Jacobian
         else:
-            passes = -(-st["D"] // 8) if st["D"] > 6 else 1   # Gaussian tables: slot-major chunks
+            passes = 2                                  # colour (plain forward or input-major) + the sample-major Jacobian
         assert launches == passes + layout  # ONE copy serves every pass
     (c0, t0, g0), (c1, t1, g1) = res[0], res[1]
     assert np.array_equal(c0, c1) and np.array_equal(t0, t1)

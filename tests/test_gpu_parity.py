@@ -46,7 +46,7 @@ def check_grad(name, got, want32, want64):
         f"{name}: rel-L2 vs fp32 oracle {e32:.2e}, vs fp64 oracle {e64:.2e}, fp32-oracle noise {noise:.2e}")
 
 
-def run_case(oracles, sc, *, volume=True, step=True, camera=True, tf=True, delayed=False):
+def run_case(oracles, sc, *, volume=True, step=True, camera=True, tf=True, delayed=False, adj_color_mask=None):
     o32, o64 = oracles
     want_c, want_t = scenes.np_forward(o32, sc)
     got_c, got_t = gr.forward(sc)
@@ -59,6 +59,8 @@ def run_case(oracles, sc, *, volume=True, step=True, camera=True, tf=True, delay
     assert mism.mean() <= 1e-3
     assert np.all(np.abs(got_t.astype(np.int64) - want_t)[mism] <= 1)
     adj_color = np.random.RandomState(7).randn(*want_c.shape).astype(np.float32)
+    if adj_color_mask is not None:
+        adj_color = adj_color * adj_color_mask(adj_color)
     kw = dict(volume=volume, step=step, camera=camera, tf=tf)
     got = gr.adjoint(sc, want_c, want_t, adj_color, delayed=delayed, **kw)
     w32 = scenes.np_adjoint(o32, sc, want_c, want_t, adj_color, **kw)
@@ -108,6 +110,22 @@ def test_large_tf_tables_shared_memory_accumulators(oracles, tfm, R, delayed):
 def test_adjoint_flag_subsets(oracles, flags):
     sc = scenes.make_scene(n=32, W=24, H=20, B=2, tf_mode=capi.TF_TEXTURE, R=8, seed=11, opacity=3.0)
     run_case(oracles, sc, **flags)
+
+
+def test_rays_with_zero_adjoint_colour_are_skipped_without_changing_results(oracles):
+    """Converged / masked pixels: the adjoint kernel skips the march of a ray whose adjoint colour is zero in all four
+    channels (its contributions are exact zeros). Half of the image, a checkerboard of pixels, and signed zeros."""
+    sc = scenes.make_scene(n=24, W=40, H=24, B=2, tf_mode=capi.TF_TEXTURE, R=8, seed=19, opacity=3.0)
+
+    def mask(a):
+        m = np.ones_like(a)
+        m[:, :, : a.shape[2] // 2] = 0.0          # left half: zero
+        m[:, ::2, 1::2] = -0.0                     # a checkerboard of negative zeros on top
+        return m
+
+    got = run_case(oracles, sc, adj_color_mask=mask)
+    assert not got["adj_step_size"][:, :, : sc.W // 2].any()
+    assert np.abs(got["adj_volume"]).max() > 0
 
 
 def test_consistency_scenes_of_the_reference(oracles):

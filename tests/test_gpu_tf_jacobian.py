@@ -1,7 +1,7 @@
 """GPU: forward-mode with TRANSFER-FUNCTION tangents in one marching pass (diffdvr_b200/csrc/dvr_tfjac.cuh) against
 the slot-major kernel it replaces (the reference's scheme, cudAD::fvar<real_t, D> in chunks of 8 slots: ceil(D / 8)
 marches) and against the oracle's restated dual numbers. The reference seeds these tangents at
-renderer/renderer_tf.cuh:121-154 (Identity), 255-288 (Texture), 436-485 (Linear)."""
+renderer/renderer_tf.cuh:121-154 (Identity), 255-288 (Texture), 436-485 (Linear), 521-560 (Gaussian)."""
 import numpy as np
 import pytest
 import torch
@@ -22,7 +22,8 @@ def _tf_slots(sc, first=0):
     return np.arange(first, first + R * C, dtype=np.int32).reshape(1, R, C)
 
 
-@pytest.mark.parametrize("tfm,R", [(capi.TF_IDENTITY, 1), (capi.TF_TEXTURE, 64), (capi.TF_TEXTURE, 2), (capi.TF_LINEAR, 7)])
+@pytest.mark.parametrize("tfm,R", [(capi.TF_IDENTITY, 1), (capi.TF_TEXTURE, 64), (capi.TF_TEXTURE, 2), (capi.TF_LINEAR, 7),
+                                   (capi.TF_GAUSSIAN, 3), (capi.TF_GAUSSIAN, 9)])
 @pytest.mark.parametrize("blend", [capi.BLEND_BEER_LAMBERT, capi.BLEND_ALPHA])
 @pytest.mark.parametrize("filt", [capi.FILTER_NEAREST, capi.FILTER_TRILINEAR])
 def test_one_pass_equals_the_slot_major_passes(tfm, R, blend, filt):
@@ -50,7 +51,7 @@ def test_one_pass_equals_the_slot_major_passes(tfm, R, blend, filt):
             assert scenes.rel_l2(g1[..., d, :], g8[..., d, :]) <= 2e-4, d
 
 
-@pytest.mark.parametrize("tfm,R", [(capi.TF_TEXTURE, 6), (capi.TF_LINEAR, 4), (capi.TF_IDENTITY, 1)])
+@pytest.mark.parametrize("tfm,R", [(capi.TF_TEXTURE, 6), (capi.TF_LINEAR, 4), (capi.TF_IDENTITY, 1), (capi.TF_GAUSSIAN, 4)])
 def test_one_pass_against_the_restated_dual_numbers(tfm, R):
     """The oracle pushes fvar<D> through the reference's kernel; D = 24 / 20 / 2 here, more than one chunk of the
     slot-major kernel."""
@@ -65,7 +66,7 @@ def test_one_pass_against_the_restated_dual_numbers(tfm, R):
     assert scenes.rel_l2(got_g * same, want_g * same) <= 1e-4
 
 
-@pytest.mark.parametrize("tfm,R", [(capi.TF_TEXTURE, 5), (capi.TF_LINEAR, 4)])
+@pytest.mark.parametrize("tfm,R", [(capi.TF_TEXTURE, 5), (capi.TF_LINEAR, 4), (capi.TF_GAUSSIAN, 3)])
 def test_slot_maps_shared_missing_and_mixed_with_ray_tangents(tfm, R):
     """Slots shared between TF entries and with a ray input add up; entries without a slot (-1) are dropped; the
     ray / stepsize tangents of the same call come from the input-major kernel and are kept."""
@@ -110,3 +111,18 @@ def test_strided_jacobian_output():
     torch.cuda.synchronize()
     assert np.array_equal(grad.cpu().numpy(), want)
     assert bool((store[..., W:] == 7.0).all())
+
+
+def test_gaussian_tables_too_large_for_the_moment_table_take_the_slot_major_passes():
+    """15 moments per row and thread in shared memory: R = 40 does not fit, the call falls back to ceil(D / 8) passes
+    and still matches the forced slot-major result bit for bit (it IS that path)."""
+    sc = scenes.make_scene(n=16, W=16, H=8, B=1, camera_mode=capi.CAMERA_REFERENCE_FRAME, tf_mode=capi.TF_GAUSSIAN, R=40,
+                           seed=5, opacity=2.0)
+    d_tf = _tf_slots(sc)
+    D = d_tf.size
+    lib = capi.load()
+    n0 = lib.launch_count()
+    _, _, g = gr.forward_gradients(sc, D, d_tf=d_tf, lib=lib)
+    assert lib.launch_count() - n0 >= (D + 7) // 8
+    _, _, g8 = gr.forward_gradients(sc, D, d_tf=d_tf, lib=lib, options=capi.make_call_options(**SLOT_MAJOR))
+    assert np.array_equal(g, g8)

@@ -100,15 +100,22 @@ def run_fwdmode_tf(reps, flush):
     dev = torch.device("cuda", 0)
     lib = capi.load()
     rows = []
-    for label, R in (("C2 scene, Texture R=64 (D=256)", 64), ("C2 scene, Texture R=8 (D=32)", 8)):
-        w = workloads.get("C2", views=1, batch=1)
-        tf = torch.from_numpy(np.ascontiguousarray(
-            workloads.synthetic.tf_texture_from_linear(workloads.synthetic.tf_linear_two_peaks(), R))).to(dev)
+    for label, R in (("C2 scene, Texture R=64 (D=256)", 64), ("C2 scene, Texture R=8 (D=32)", 8),
+                     ("C3 scene (one 512^2 view), Gaussian R=4 (D=24)", -4)):
+        if R > 0:
+            w = workloads.get("C2", views=1, batch=1)
+            tf = torch.from_numpy(np.ascontiguousarray(
+                workloads.synthetic.tf_texture_from_linear(workloads.synthetic.tf_linear_two_peaks(), R))).to(dev)
+            C = 4
+        else:
+            w = workloads.get("C3", views=1, batch=1)
+            R, C = -R, 6
+            tf = torch.from_numpy(np.ascontiguousarray(w.tf())).to(dev)
         inp = w.inputs(lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev), views=[0], tf=tf)
         ws = lib.workspace()
         ws.set_volume(inp.volume)
-        D = R * 4
-        d_tf = torch.arange(D, dtype=torch.int32, device=dev).reshape(1, R, 4)
+        D = R * C
+        d_tf = torch.arange(D, dtype=torch.int32, device=dev).reshape(1, R, C)
         st = capi.make_fd_settings(D, d_tf=d_tf, has_tf_derivatives=True)
         color = torch.empty(1, w.res, w.res, 4, device=dev)
         term = torch.empty(1, w.res, w.res, dtype=torch.int32, device=dev)
