@@ -369,7 +369,8 @@ def run_ours(a):
     result_host = torch.empty(max(1, (adj_tf.numel() if has_tf else 0)) + 1).pin_memory()
     per_ray_host = None
     if fwd_mode:  # C3's result is per-ray: the camera gradients of this rank's views
-        per_ray_host = torch.empty(len(my_views), H, W, 6).pin_memory()
+        # two contiguous pinned buffers (a strided destination would take the slow element-wise copy path)
+        per_ray_host = (torch.empty(len(my_views), H, W, 3).pin_memory(), torch.empty(len(my_views), H, W, 3).pin_memory())
     image_host = torch.empty(len(my_views), H, W, 4).pin_memory() if not w.adjoint and not fwd_mode else None
 
     def step_fn(e2e: bool, record: bool):
@@ -430,8 +431,8 @@ def run_ours(a):
                 adj = capi.make_adjoint_outputs(adj_camera_ray_start=adj_rs[:nb], adj_camera_ray_dir=adj_rd[:nb])
                 lib.forward_variables_to_gradients(jac[:nb], adj_color, fd, adj, stream)
                 if e2e:
-                    per_ray_host[k * w.batch:k * w.batch + nb, ..., :3].copy_(adj_rs[:nb], non_blocking=True)
-                    per_ray_host[k * w.batch:k * w.batch + nb, ..., 3:].copy_(adj_rd[:nb], non_blocking=True)
+                    per_ray_host[0][k * w.batch:k * w.batch + nb].copy_(adj_rs[:nb], non_blocking=True)
+                    per_ray_host[1][k * w.batch:k * w.batch + nb].copy_(adj_rd[:nb], non_blocking=True)
             else:
                 adj = capi.make_adjoint_outputs(adj_volume=adj_volume, adj_tf=adj_tf,
                                                 adj_step_size=adj_steps[:nb] if has_step else None,
@@ -562,6 +563,11 @@ def run_ours(a):
     # HBM view of the same kernel: algorithmic bytes and measured DRAM traffic against the copy peak
     alg_bytes = 32.0 * cells_per_launch + (64.0 * cells_per_launch if (dom == "adjoint" and has_vol) else 0.0) + \
         rays_per_launch * (36.0 if dom == "adjoint" else 20.0 + (16.0 * D if fwd_mode else 0.0))
+    # what the ncu capture of this kernel says about the unit that does bound it (gather / RED ceilings only bound the
+    # kernels whose per-sample arithmetic is light: C4; the TF- and ray-gradient kernels are bound by issue slots)
+    roof.update(issue_slots_busy_pct=prof.get("issue_active_pct"), lanes_per_instruction=prof.get("lanes_per_inst"),
+                thread_instructions_per_sample=prof.get("thread_inst_per_sample"),
+                registers=prof.get("registers"), warps_active_pct=prof.get("warps_active_pct"))
     roof.update(algorithmic_bytes_per_launch=alg_bytes, hbm_peak_gbs=hbm_peak,
                 hbm_peak_source="MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650",
                 algorithmic_gbs=alg_bytes / (dom_ms * 1e-3) / 1e9,

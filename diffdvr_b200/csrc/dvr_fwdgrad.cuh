@@ -295,13 +295,36 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
   smp.init(in, b, nullptr, 0);
   int i = 0;
   float fi = 0.f;
+  constexpr bool LOOKAHEAD = FILTER == kFilterTrilinearQuad && DVR_LOOKAHEAD_RAY;
+  // look-ahead state (Sampler::lookahead): parameter and position of the NEXT sample, its cell already requested
+  [[maybe_unused]] float tNext = sample_t(ray, 0.f);
+  [[maybe_unused]] f3 pNext = {0.f, 0.f, 0.f};
+  [[maybe_unused]] unsigned qn = 0u;
+  if constexpr (LOOKAHEAD) {
+    pNext = sample_pos<true>(ray, tNext);
+    if (!(tNext > ray.tmax)) smp.lookahead(in, pNext.x, pNext.y, pNext.z, qn);
+  }
   for (;; ++i, fi += 1.0f) {
-    const float t = sample_t(ray, fi);
+    float t;
+    f3 p;
+    if constexpr (LOOKAHEAD) t = tNext;
+    else t = sample_t(ray, fi);
     if (t > ray.tmax) break;
     if (acc.w > in.earlyOut) break;
-    const f3 p = sample_pos<true>(ray, t);
-    const float density = smp.fetch(in, nullptr, p.x, p.y, p.z);
-    if constexpr (DVR_PREFETCH_RAY) {
+    float density;
+    [[maybe_unused]] f3 gCell = {0.f, 0.f, 0.f};
+    if constexpr (LOOKAHEAD) {
+      p = pNext;
+      density = smp.interp(p.x, p.y, p.z);
+      gCell = smp.unit_gradient();
+      tNext = sample_t(ray, fi + 1.0f);
+      pNext = sample_pos<true>(ray, tNext);
+      if (!(tNext > ray.tmax)) smp.lookahead(in, pNext.x, pNext.y, pNext.z, qn);
+    } else {
+      p = sample_pos<true>(ray, t);
+      density = smp.fetch(in, nullptr, p.x, p.y, p.z);
+    }
+    if constexpr (DVR_PREFETCH_RAY && !LOOKAHEAD) {
       const f3 pn = sample_pos<false>(ray, sample_t(ray, fi + 1.0f));
       smp.prefetch_cell(in, pn.x, pn.y, pn.z);
     }
@@ -311,7 +334,9 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
 #pragma unroll
       for (int j = 0; j < NP; ++j) dd[j] = make_float2(0.f, 0.f);  // no positional tangent (interpolation.cuh:52-65)
     } else {
-      const f3 g = smp.template adjoint<true>(1.0f);  // gradient of the trilinear cell at the sample
+      f3 g;  // gradient of the trilinear cell at the sample
+      if constexpr (LOOKAHEAD) g = gCell;
+      else g = smp.template adjoint<true>(1.0f);
       const float d0 = g.x * ray.invVoxel.x, d1 = g.y * ray.invVoxel.y, d2 = g.z * ray.invVoxel.z;
       dd[0] = make_float2(d0, d1);
       dd[1] = make_float2(d2, t * d0);

@@ -27,7 +27,34 @@ __global__ void __launch_bounds__(kThreads) k_forward(const RayInputs in, const 
   smp.init(in, b, nullptr, 0);
   f4 acc = {0.f, 0.f, 0.f, 0.f};
   float fi = 0.f;  // sample counter; exact in fp32 (terminationIndex < 2^24)
-  if constexpr (TF == kTfIdentity) {
+  if constexpr (FILTER == kFilterTrilinearQuad && DVR_LOOKAHEAD) {
+    // look-ahead loop (Sampler::lookahead): same samples, same arithmetic, the next cell's loads issued one sample early
+    [[maybe_unused]] const float sa = smem[0], sc = smem[1];
+    unsigned qn;
+    float t = sample_t(ray, 0.f);
+    f3 p = sample_pos<false>(ray, t);
+    if (!(t > ray.tmax)) smp.lookahead(in, p.x, p.y, p.z, qn);
+    for (;;) {
+      if (t > ray.tmax) break;
+      if (acc.w > in.earlyOut) break;
+      const float density = smp.interp(p.x, p.y, p.z);
+      fi += 1.0f;
+      t = sample_t(ray, fi);
+      p = sample_pos<false>(ray, t);
+      if (!(t > ray.tmax)) smp.lookahead(in, p.x, p.y, p.z, qn);
+      if constexpr (TF == kTfIdentity) {
+        const float dc = fmaxf(0.f, fminf(density, 1.f));
+        const float alpha = blend_alpha<BLEND>(dc * sa, ray.step);
+        const float om = 1.f - acc.w;
+        acc.x = fmaf(om * (dc * sc), alpha, acc.x);
+        acc.w = fmaf(om, alpha, acc.w);
+      } else {
+        const f4 cur = tf_eval<TF>(smem, in.R, density);
+        acc = blend_over(acc, cur, blend_alpha<BLEND>(cur.w, ray.step));
+      }
+    }
+    if constexpr (TF == kTfIdentity) acc.y = acc.z = acc.x;
+  } else if constexpr (TF == kTfIdentity) {
     // r = g = b for this TF (renderer_tf.cuh:62-73): march one colour channel; the table's two
     // scales stay in registers
     const float sa = smem[0], sc = smem[1];
@@ -441,22 +468,55 @@ __global__ void __launch_bounds__(kThreads, adjoint_min_ctas<TF, HAS_VOL, TFACC,
     [[maybe_unused]] const f3 p0 = {fmaf(ray.tmin, ray.pd.x, ray.ps.x), fmaf(ray.tmin, ray.pd.y, ray.ps.y),
                                     fmaf(ray.tmin, ray.pd.z, ray.ps.z)};
     [[maybe_unused]] const f3 dp = {ray.step * ray.pd.x, ray.step * ray.pd.y, ray.step * ray.pd.z};
+    // Look-ahead cell loads (Sampler::lookahead): measured per config (profiles/r02_lookahead.md) -- C2 adjoint(tf)
+    // 3.52 -> 3.35 ms, C3 adjoint(camera) 20.1 -> 18.9, C5 adjoint(volume + tf + stepsize) 30.2 -> 28.3; the lean
+    // Identity-TF adjoint(volume) of C4 is the exception (7.04 -> 7.27 ms: the gradient flush becomes a second divergent
+    // region at the bottom of an iteration that has little arithmetic to hide a load under), so it keeps fetch().
+    constexpr bool LOOKAHEAD = FILTER == kFilterTrilinearQuad && (HAS_RAY ? DVR_LOOKAHEAD_RAY : DVR_LOOKAHEAD_ADJ) &&
+                               !(TF == kTfIdentity && HAS_VOL && !HAS_RAY);
+    // position of sample number f (and its ray parameter t for the kernels that differentiate the ray)
+    auto position = [&](float f, float& tOut) -> f3 {
+      if constexpr (HAS_RAY) {
+        tOut = sample_t(ray, f);
+        return sample_pos<true>(ray, tOut);
+      } else {
+        tOut = 0.f;
+        const float2 xy = pk_fma(f, make_float2(dp.x, dp.y), make_float2(p0.x, p0.y));
+        return {xy.x, xy.y, fmaf(f, dp.z, p0.z)};
+      }
+    };
+    // look-ahead state (Sampler::lookahead): position of the sample the loop is at, already inside the cached cell
+    [[maybe_unused]] float tCur = 0.f;
+    [[maybe_unused]] f3 pCur = {0.f, 0.f, 0.f};
+    if constexpr (LOOKAHEAD) {
+      if (fi >= 0.f) {
+        pCur = position(fi, tCur);
+        unsigned q0 = 0u;
+        smp.lookahead(in, pCur.x, pCur.y, pCur.z, q0);  // first cell: loads unconditionally (no cell cached yet)
+        smp.qoff = q0;
+      }
+    }
     for (; fi >= 0.f; fi -= 1.0f) {  // fi counts n-1 .. 0 exactly (n < 2^24)
       float t = 0.f;
       f3 p;
-      if constexpr (HAS_RAY) {
-        t = sample_t(ray, fi);
-        p = sample_pos<true>(ray, t);
-      } else {
-        const float2 xy = pk_fma(fi, make_float2(dp.x, dp.y), make_float2(p0.x, p0.y));
-        p = {xy.x, xy.y, fmaf(fi, dp.z, p0.z)};
-      }
-      const float density = smp.fetch(in, &aa, p.x, p.y, p.z);
-      if constexpr (HAS_RAY ? DVR_PREFETCH_RAY : DVR_PREFETCH_ADJ) {
-        // the next sample's position in the cheap form (a prefetch may guess wrong next to a cell face)
+      float density;
+      [[maybe_unused]] f3 gUnit = {0.f, 0.f, 0.f};
+      [[maybe_unused]] bool cellChanges = false;
+      [[maybe_unused]] unsigned qNext = 0u;
+      if constexpr (LOOKAHEAD) {
+        t = tCur;
+        p = pCur;
+        density = smp.interp(p.x, p.y, p.z);
+        if constexpr (HAS_RAY) gUnit = smp.unit_gradient();
+        // the corner registers are dead from here on: the previous sample's cell loads run under this sample's arithmetic
         const float fn = fi - 1.0f;
-        const float2 xy = pk_fma(fn, make_float2(dp.x, dp.y), make_float2(p0.x, p0.y));
-        smp.prefetch_cell(in, xy.x, xy.y, fmaf(fn, dp.z, p0.z));
+        if (fn >= 0.f) {
+          pCur = position(fn, tCur);
+          cellChanges = smp.lookahead(in, pCur.x, pCur.y, pCur.z, qNext);
+        }
+      } else {
+        p = position(fi, t);
+        density = smp.fetch(in, &aa, p.x, p.y, p.z);
       }
       float adjDensity, adjStepBlend;
       if constexpr (TF == kTfIdentity) {
@@ -480,7 +540,13 @@ __global__ void __launch_bounds__(kThreads, adjoint_min_ctas<TF, HAS_VOL, TFACC,
         blend_adjoint<BLEND, false>(acc, adjAcc, cur, ray.step, adjCur, adjStepBlend);
         adjDensity = tf_adjoint<TF, TFACC>(s_tf, in.R, density, adjCur, tfg, tfCache);
       }
-      const f3 g = smp.template adjoint<HAS_RAY>(adjDensity);
+      f3 g;
+      if constexpr (LOOKAHEAD) {
+        smp.accumulate(adjDensity);
+        g = {adjDensity * gUnit.x, adjDensity * gUnit.y, adjDensity * gUnit.z};
+      } else {
+        g = smp.template adjoint<HAS_RAY>(adjDensity);
+      }
       if constexpr (RAY == kRayStep) {
         // d pos / d stepsize = i dir / voxel = i pd: one dot product and one accumulator
         adjStep = aa.compatStepOverwrite ? adjStepBlend : adjStep + adjStepBlend;
@@ -493,6 +559,12 @@ __global__ void __launch_bounds__(kThreads, adjoint_min_ctas<TF, HAS_VOL, TFACC,
         adjDir.x = fmaf(w.x, t, adjDir.x); adjDir.y = fmaf(w.y, t, adjDir.y); adjDir.z = fmaf(w.z, t, adjDir.z);
         const float adjT = w.x * ray.dir.x + w.y * ray.dir.y + w.z * ray.dir.z;
         adjStep = fmaf(adjT, fi, adjStep);
+      }
+      if constexpr (LOOKAHEAD) {
+        if (cellChanges) {  // the gradient of the cell this sample was in goes out before the next cell is adopted
+          smp.flush(&aa);
+          smp.qoff = qNext;
+        }
       }
     }
     smp.flush(&aa);

@@ -116,11 +116,32 @@ __global__ void __launch_bounds__(kThreads, 4) k_tf_jacobian(const RayInputs in,
   smp.init(in, b, nullptr, 0);
   f4 acc = {0.f, 0.f, 0.f, 0.f};
   float fi = 0.f;
+  constexpr bool LOOKAHEAD = FILTER == kFilterTrilinearQuad && DVR_LOOKAHEAD;
+  // the positions of the kernel that wrote `fwd` (uniform branch), so that the accumulator ends at `fin`
+  auto position = [&](float f) -> f3 {
+    const float t = sample_t(ray, f);
+    return ga.exactPos ? sample_pos<true>(ray, t) : sample_pos<false>(ray, t);
+  };
+  [[maybe_unused]] f3 pNext = {0.f, 0.f, 0.f};
+  [[maybe_unused]] unsigned qn = 0u;
+  if constexpr (LOOKAHEAD) {
+    if (n > 0) {
+      pNext = position(0.f);
+      smp.lookahead(in, pNext.x, pNext.y, pNext.z, qn);
+    }
+  }
   for (int i = 0; i < n; ++i, fi += 1.0f) {
-    const float t = sample_t(ray, fi);
-    // the positions of the kernel that wrote `fwd` (uniform branch), so that the accumulator ends at `fin`
-    const f3 p = ga.exactPos ? sample_pos<true>(ray, t) : sample_pos<false>(ray, t);
-    const float density = smp.fetch(in, nullptr, p.x, p.y, p.z);
+    float density;
+    if constexpr (LOOKAHEAD) {
+      density = smp.interp(pNext.x, pNext.y, pNext.z);
+      if (i + 1 < n) {  // the next sample's cell loads run under this sample's arithmetic (Sampler::lookahead)
+        pNext = position(fi + 1.0f);
+        smp.lookahead(in, pNext.x, pNext.y, pNext.z, qn);
+      }
+    } else {
+      const f3 p = position(fi);
+      density = smp.fetch(in, nullptr, p.x, p.y, p.z);
+    }
     [[maybe_unused]] TfCache<TF> tfc;
     f4 cur;
     if constexpr (TF == kTfGaussian) cur = tf_eval_cached<TF>(s_tf, in.R, density, tfc);  // the values of tf_eval

@@ -290,11 +290,10 @@ typedef struct DvrCallOptions {
   int64_t max_scratch_bytes;         /* cap on the per-call / workspace QUAD buffers of this call; above it the call
                                         takes the in-place path (counted, see dvr_get_stat). <= 0: 16 GiB */
   DvrWorkspace* workspace;           /* may be NULL */
-  int32_t forward_mode_tf;           /* forward-mode with TF tangents: 0 automatic (Identity / Texture / Linear tables:
-                                        ONE sample-major marching pass for any D, csrc/dvr_tfjac.cuh; Gaussian:
-                                        ceil(D / 8) slot-major passes), 1 always the slot-major passes (the reference's
-                                        scheme in chunks; kept for A/B measurements). Read only when struct_size
-                                        covers it (a 32-byte DvrCallOptions of ABI 2.0 stays valid) */
+  int32_t forward_mode_tf;           /* forward-mode with TF tangents: 0 automatic (ONE sample-major marching pass for any
+                                        D, csrc/dvr_tfjac.cuh; Gaussian tables of more than 28 rows: ceil(D / 8)
+                                        slot-major passes), 1 always the slot-major passes (the reference's scheme in
+                                        chunks; kept for A/B measurements). Read only when struct_size covers it */
   int32_t reserved0;
 } DvrCallOptions;
 
