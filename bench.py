@@ -62,6 +62,10 @@ def parse_args():
     p.add_argument("--batch", type=int, default=None, help="views per kernel launch")
     p.add_argument("--step-voxels", type=float, default=None)
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--skip-zero-rays", action="store_true",
+                   help="adjoint: let the library skip the rays whose adjoint colour is zero in all channels (its default: "
+                        "their contributions are exact zeros). The bench marches every ray unless this is given, like the "
+                        "reference arm does, so that both arms do the same work")
     p.add_argument("--no-workspace", action="store_true",
                    help="per-call QUAD scratch (copy rebuilt, gradient scratch zeroed and folded on every call)")
     return p.parse_args()
@@ -338,7 +342,8 @@ def run_ours(a):
 
     stream = torch.cuda.current_stream().cuda_stream
     ws = None if a.no_workspace else lib.workspace()
-    opts = capi.make_call_options(workspace=ws, compat_stepsize_overwrite=False)
+    opts = capi.make_call_options(workspace=ws, compat_stepsize_overwrite=False,
+                                  adjoint_march_zero_rays=not a.skip_zero_rays)
 
     # targets: renders of the ground truth (set-up, untimed)
     truth_dev = truth.to(dev)
@@ -502,20 +507,38 @@ def run_ours(a):
 
     # ---- accounting: samples, cell visits --------------------------------------------------------
     counts = torch.zeros(2, dtype=torch.int64, device=dev)
+    counts_adj = torch.zeros(2, dtype=torch.int64, device=dev)   # samples / cells of the rays the adjoint marches
+    rays_total = rays_skipped = 0
     tmp_c = torch.empty(w.batch, H, W, 4, device=dev)
     tmp_t = torch.empty(w.batch, H, W, dtype=torch.int32, device=dev)
     for k, idx in enumerate(launches):
         inp = inputs(volume, tf_dev, cam_dev[k], idx)
         if keep_images:
-            t = terms[k][:len(idx)]
+            c, t = colors[k][:len(idx)], terms[k][:len(idx)]
         else:
             lib.render_forward(inp, tmp_c[:len(idx)], tmp_t[:len(idx)], stream, opts)
-            t = tmp_t[:len(idx)]
+            c, t = tmp_c[:len(idx)], tmp_t[:len(idx)]
         lib.count_cell_visits(inp, t, counts, stream)
+        if w.adjoint and not fwd_mode:
+            # the adjoint skips a ray whose adjoint colour is zero in all channels (sign(0) of an L1 loss where the
+            # render already equals the target): count what it does march
+            if w.name == "C4":
+                zero = (c[..., 3] - targets[k]) == 0
+            else:
+                zero = ((c - targets[k]) == 0).all(dim=-1)
+            marched = torch.where(zero, torch.zeros_like(t), t) if a.skip_zero_rays else t
+            lib.count_cell_visits(inp, marched.contiguous(), counts_adj, stream)
+            rays_total += int(zero.numel())
+            rays_skipped += int((zero & (t > 0)).sum()) if a.skip_zero_rays else 0
     torch.cuda.synchronize()
     if world > 1:
         dist.all_reduce(counts)
+        dist.all_reduce(counts_adj)
+        rr = torch.tensor([rays_total, rays_skipped], dtype=torch.int64, device=dev)
+        dist.all_reduce(rr)
+        rays_total, rays_skipped = int(rr[0]), int(rr[1])
     n_samples, n_cells = int(counts[0]), int(counts[1])
+    n_samples_adj, n_cells_adj = int(counts_adj[0]), int(counts_adj[1])
     fwd_ms = float(np.mean([s.elapsed_time(e) for s, e in fwd_ev]))
     adj_ms = float(np.mean([s.elapsed_time(e) for s, e in adj_ev])) if adj_ev else None
     n_launch_total = sum(len(list(multigpu.batches(multigpu.shard_views(w.views, r, world), w.batch)))
@@ -523,6 +546,8 @@ def run_ours(a):
     rays_per_launch = w.batch * H * W
     cells_per_launch = n_cells / n_launch_total
     samples_per_launch = n_samples / n_launch_total
+    adj_cells_per_launch = n_cells_adj / n_launch_total if (w.adjoint and not fwd_mode) else cells_per_launch
+    adj_samples_per_launch = n_samples_adj / n_launch_total if (w.adjoint and not fwd_mode) else samples_per_launch
 
     # ---- roofline of the dominant kernel against the MEASURED gather / RED ceilings ----------------
     peaks = load_json("MEASURED_PEAKS.json") or {}
@@ -539,6 +564,8 @@ def run_ours(a):
     else:
         dom, dom_ms = "forward", fwd_ms
         kernel = f"k_forward<TrilinearQuad,{w.tf_kind},BeerLambert>"
+    if dom == "adjoint":   # the roofline counts the cells the kernel DID visit
+        cells_per_launch = adj_cells_per_launch
     prof = ncu.get(f"{w.name}:{dom}") or {}
     roof = {"kernel": kernel, "bound": prof.get("bound", "issue"),
             "bound_source": prof.get("source", "ncu --set full of this kernel (profiles/): issue slots, not DRAM"),
@@ -595,7 +622,10 @@ def run_ours(a):
             "steps": a.steps, "warmup": warm, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
             "fwd_gsamples_per_s": samples_per_launch / (fwd_ms * 1e-3) / 1e9,
-            "adj_gsamples_per_s": samples_per_launch / (adj_ms * 1e-3) / 1e9 if adj_ms else None,
+            "adj_gsamples_per_s": adj_samples_per_launch / (adj_ms * 1e-3) / 1e9 if adj_ms else None,
+            "adjoint_rays_skipped": {"rays_with_zero_adjoint_colour_and_samples": rays_skipped, "rays": rays_total,
+                                     "samples_marched_frac": (n_samples_adj / n_samples) if n_samples else None,
+                                     "march_all_rays": not a.skip_zero_rays} if (w.adjoint and not fwd_mode) else None,
             "fwd_ms_per_launch": fwd_ms, "adj_ms_per_launch": adj_ms,
             "samples_per_step": n_samples, "cell_visits_per_step": n_cells,
             "roofline": roof,

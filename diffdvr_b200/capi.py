@@ -102,12 +102,13 @@ class DvrCallOptions(ctypes.Structure):
         ("max_scratch_bytes", ctypes.c_int64),
         ("workspace", ctypes.c_void_p),
         ("forward_mode_tf", ctypes.c_int32),
-        ("reserved0", ctypes.c_int32),
+        ("adjoint_march_zero_rays", ctypes.c_int32),
     ]
 
 
 def make_call_options(volume_layout: int = -1, compat_stepsize_overwrite: bool = False, sync: bool = False,
-                      max_scratch_bytes: int = 0, workspace=None, forward_mode_tf: int = 0) -> DvrCallOptions:
+                      max_scratch_bytes: int = 0, workspace=None, forward_mode_tf: int = 0,
+                      adjoint_march_zero_rays: bool = False) -> DvrCallOptions:
     o = DvrCallOptions()
     o.struct_size = ctypes.sizeof(DvrCallOptions)
     o.volume_layout = int(volume_layout)
@@ -116,6 +117,7 @@ def make_call_options(volume_layout: int = -1, compat_stepsize_overwrite: bool =
     o.max_scratch_bytes = int(max_scratch_bytes)
     o.workspace = workspace.handle if workspace is not None else None
     o.forward_mode_tf = int(forward_mode_tf)   # 1: the slot-major ceil(D/8)-pass kernel (A/B measurements)
+    o.adjoint_march_zero_rays = int(bool(adjoint_march_zero_rays))  # 1: no skipping of rays with zero adjoint colour
     o._keep = workspace
     return o
 

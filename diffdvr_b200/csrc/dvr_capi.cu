@@ -32,6 +32,7 @@ struct CallCtx {
   long long cap = 16ll << 30;
   DvrWorkspace* ws = nullptr;
   bool fwdTfSlotMajor = false;
+  bool marchZeroRays = false;
 };
 
 struct Fail {
@@ -90,6 +91,8 @@ CallCtx resolve_options(const DvrCallOptions* o) {
       fail(DVR_ERR_INVALID_ARGUMENT, "forward_mode_tf must be 0 or 1, but is %d", o->forward_mode_tf);
     c.fwdTfSlotMajor = o->forward_mode_tf == 1;
   }
+  if (o->struct_size >= offsetof(DvrCallOptions, adjoint_march_zero_rays) + sizeof(int32_t))
+    c.marchZeroRays = o->adjoint_march_zero_rays != 0;
   if (o->volume_layout < -1 || o->volume_layout > 1)
     fail(DVR_ERR_INVALID_ARGUMENT, "volume_layout must be -1, 0 or 1, but is %d", o->volume_layout);
   c.layout = o->volume_layout;
@@ -698,6 +701,7 @@ int dvr_render_adjoint_ex(const DvrInputs* inputs, const DvrOutputs* fwd, const 
     const bool hasRay = aa.hasStep || aa.hasCam;
     if (!hasVol && !hasTf && !hasRay) fail(DVR_ERR_INVALID_ARGUMENT, "At least one adjoint variable must be activated!");
     aa.compatStepOverwrite = ctx.compat;
+    aa.marchZeroRays = ctx.marchZeroRays;
     aa.sameStrides = hasVol && aa.avx == c.ri.sx && aa.avy == c.ri.sy && aa.avz == c.ri.sz;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (preshaded) {

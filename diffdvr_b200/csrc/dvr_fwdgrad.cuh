@@ -298,15 +298,15 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
   constexpr bool LOOKAHEAD = FILTER == kFilterTrilinearQuad && DVR_LOOKAHEAD_RAY;
   // look-ahead state (Sampler::lookahead): parameter and position of the NEXT sample, its cell already requested
   [[maybe_unused]] float tNext = sample_t(ray, 0.f);
-  [[maybe_unused]] f3 pNext = {0.f, 0.f, 0.f};
-  [[maybe_unused]] unsigned qn = 0u;
   if constexpr (LOOKAHEAD) {
-    pNext = sample_pos<true>(ray, tNext);
-    if (!(tNext > ray.tmax)) smp.lookahead(in, pNext.x, pNext.y, pNext.z, qn);
+    if (!(tNext > ray.tmax)) {
+      const f3 pn = sample_pos<true>(ray, tNext);
+      smp.lookahead_f(in, pn.x, pn.y, pn.z);
+    }
   }
   for (;; ++i, fi += 1.0f) {
     float t;
-    f3 p;
+    [[maybe_unused]] f3 p;
     if constexpr (LOOKAHEAD) t = tNext;
     else t = sample_t(ray, fi);
     if (t > ray.tmax) break;
@@ -314,12 +314,13 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
     float density;
     [[maybe_unused]] f3 gCell = {0.f, 0.f, 0.f};
     if constexpr (LOOKAHEAD) {
-      p = pNext;
-      density = smp.interp(p.x, p.y, p.z);
-      gCell = smp.unit_gradient();
+      density = smp.interp_f();
+      gCell = smp.unit_gradient();   // from the same corner values and fractions, before either is overwritten
       tNext = sample_t(ray, fi + 1.0f);
-      pNext = sample_pos<true>(ray, tNext);
-      if (!(tNext > ray.tmax)) smp.lookahead(in, pNext.x, pNext.y, pNext.z, qn);
+      if (!(tNext > ray.tmax)) {
+        const f3 pn = sample_pos<true>(ray, tNext);
+        smp.lookahead_f(in, pn.x, pn.y, pn.z);
+      }
     } else {
       p = sample_pos<true>(ray, t);
       density = smp.fetch(in, nullptr, p.x, p.y, p.z);

@@ -30,18 +30,21 @@ __global__ void __launch_bounds__(kThreads) k_forward(const RayInputs in, const 
   if constexpr (FILTER == kFilterTrilinearQuad && DVR_LOOKAHEAD) {
     // look-ahead loop (Sampler::lookahead): same samples, same arithmetic, the next cell's loads issued one sample early
     [[maybe_unused]] const float sa = smem[0], sc = smem[1];
-    unsigned qn;
     float t = sample_t(ray, 0.f);
-    f3 p = sample_pos<false>(ray, t);
-    if (!(t > ray.tmax)) smp.lookahead(in, p.x, p.y, p.z, qn);
+    if (!(t > ray.tmax)) {
+      const f3 p = sample_pos<false>(ray, t);
+      smp.lookahead_f(in, p.x, p.y, p.z);
+    }
     for (;;) {
       if (t > ray.tmax) break;
       if (acc.w > in.earlyOut) break;
-      const float density = smp.interp(p.x, p.y, p.z);
+      const float density = smp.interp_f();
       fi += 1.0f;
       t = sample_t(ray, fi);
-      p = sample_pos<false>(ray, t);
-      if (!(t > ray.tmax)) smp.lookahead(in, p.x, p.y, p.z, qn);
+      if (!(t > ray.tmax)) {
+        const f3 p = sample_pos<false>(ray, t);
+        smp.lookahead_f(in, p.x, p.y, p.z);
+      }
       if constexpr (TF == kTfIdentity) {
         const float dc = fmaxf(0.f, fminf(density, 1.f));
         const float alpha = blend_alpha<BLEND>(dc * sa, ray.step);
@@ -159,9 +162,30 @@ struct TfGrad {
   // kTfAccSmem, Texture / Linear: the sample lies between rows (key, key + 1) with weights (1 - w, w); v = adjoint of
   // the interpolated value. One compare per sample, the products fused into the accumulation (the reference: 8
   // global atomics per sample, renderer_tf.cuh:208-216).
+  // one row of the window into the shared table (k = 0: row `base`, k = 1: row `base + 1`; Texture rows clamp)
+  DVR_DEV void flush_one(int k) {
+    int r = base + k;
+    if constexpr (TF == kTfTexture) r = min(max(r, 0), rows - 1);
+#pragma unroll
+    for (int c = 0; c < CH; ++c) {
+      const float v = k ? row[1][c] : row[0][c];
+      if (v != 0.f) atomicAdd(table + r * CH + c, v);
+    }
+  }
   DVR_DEV void add_pair(int key, const float* v, float w) {
     if (key != base) {
-      flush_rows();
+      // the density usually drifts into the NEIGHBOURING row pair: one row of the window stays, only the other goes out
+      if (key == base + 1) {
+        flush_one(0);
+#pragma unroll
+        for (int c = 0; c < CH; ++c) { row[0][c] = row[1][c]; row[1][c] = 0.f; }
+      } else if (key == base - 1) {
+        flush_one(1);
+#pragma unroll
+        for (int c = 0; c < CH; ++c) { row[1][c] = row[0][c]; row[0][c] = 0.f; }
+      } else {
+        flush_rows();
+      }
       base = key;
     }
     const float w0 = 1.f - w;
@@ -392,15 +416,14 @@ DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC
 enum : int { kRayNone = 0, kRayStep = 1, kRayCam = 2 };
 
 // Resident CTAs the register allocation aims for. Instances that differentiate the ray: 6 CTAs/SM (<= 80 registers;
-// C3 adjoint(camera) 26.2 -> 24.8 ms). The full-flag instance of C5 (volume + TF + stepsize) is latency-sensitive
-// rather than purely issue-bound (issue slots 70 % busy, profiles/r02_ncu_kernels.md): measured at 4 CTAs / 108
-// registers 39.1 ms, 5 CTAs / 96 registers 33.0 ms, 6 CTAs / 80 registers 30.9 ms (with 8 bytes of stack; the first
-// version of this instance spilled 32 bytes under the same cap and took 36.3 ms -- the TF cache, the stepsize-only
-// ray mode and the factored blend adjoint removed the pressure). Register accumulators of a Gaussian table and the
-// GaussianLog adjoint need 4 CTAs (<= 128 registers) to stay out of local memory. Forcing more CTAs on the instances
-// without ray gradients (forward <= 40 registers, adjoint(volume) <= 48) was measured and is slower.
+// C3 adjoint(camera) 26.2 -> 24.8 ms). The full-flag instance of C5 (volume + TF + stepsize), measured: before the
+// look-ahead loads 4 CTAs / 108 registers 39.1 ms, 5 / 96 33.0 ms, 6 / 80 30.9 ms (8 bytes of stack; the first version
+// of this instance spilled 32 bytes under that cap and took 36.3 ms); with the look-ahead loads (which carry the next
+// sample's position) 6 / 80 spills 16 bytes: 28.1 ms, 5 / 96 without spills: 27.7 ms -> 5. Register accumulators of a
+// Gaussian table and the GaussianLog adjoint need 4 CTAs (<= 128 registers) to stay out of local memory. Forcing more
+// CTAs on the instances without ray gradients (forward <= 40 registers, adjoint(volume) <= 48) was measured and is slower.
 #ifndef DVR_ADJ_CTAS_2
-#define DVR_ADJ_CTAS_2 6   // ray gradients + volume + TF state: <= 80 registers (8 bytes of stack in the C5 instance)
+#define DVR_ADJ_CTAS_2 5   // ray gradients + volume + TF state: <= 96 registers
 #endif
 #ifndef DVR_ADJ_CTAS_1
 #define DVR_ADJ_CTAS_1 6   // ray gradients + one of the two: <= 80 registers
@@ -411,7 +434,9 @@ constexpr int adjoint_min_ctas() {
   // register accumulators of a Gaussian table (up to kRegRows x 6 floats of state): <= 128 registers
   if ((TFACC == kTfAccReg && TF == kTfGaussian) || TF == kTfGaussianLog) return 4;
   const int extra = (HAS_VOL ? 1 : 0) + (TFACC != kTfAccNone ? 1 : 0);
-  return extra == 2 ? DVR_ADJ_CTAS_2 : (extra == 1 ? DVR_ADJ_CTAS_1 : 6);
+  // the Linear TF's gradient window carries two more registers per row (the control-point positions): one CTA fewer
+  const int linear = (TF == kTfLinear && TFACC != kTfAccNone) ? 1 : 0;
+  return (extra == 2 ? DVR_ADJ_CTAS_2 : (extra == 1 ? DVR_ADJ_CTAS_1 : 6)) - linear;
 }
 
 template <int FILTER, int TF, int BLEND, bool HAS_VOL, int TFACC, int RAY>
@@ -447,8 +472,8 @@ __global__ void __launch_bounds__(kThreads, adjoint_min_ctas<TF, HAS_VOL, TFACC,
     int n = __ldg(aa.term + b * aa.tB + y * aa.tY + x * aa.tX);
     // A ray whose adjoint colour is zero in all four channels contributes exact zeros to every output (converged or
     // masked pixels of a reconstruction): skip its march. The per-ray outputs below are still written (as zeros).
-    if (((__float_as_uint(adjAcc.x) | __float_as_uint(adjAcc.y) | __float_as_uint(adjAcc.z) | __float_as_uint(adjAcc.w)) &
-         0x7fffffffu) == 0u)
+    if (!aa.marchZeroRays && ((__float_as_uint(adjAcc.x) | __float_as_uint(adjAcc.y) | __float_as_uint(adjAcc.z) |
+                               __float_as_uint(adjAcc.w)) & 0x7fffffffu) == 0u)
       n = 0;
     float adjStep = 0.f;
     f3 adjStart = {0.f, 0.f, 0.f}, adjDir = {0.f, 0.f, 0.f};

@@ -92,6 +92,7 @@ struct AdjointArgs {
   long long atB, atR, atC;
   int hasStep, hasCam;
   int compatStepOverwrite;           // see include/dvr_b200.h
+  int marchZeroRays;                 // 1: march rays whose adjoint colour is all zero too (DvrCallOptions)
 };
 
 struct ForwardGradArgs {

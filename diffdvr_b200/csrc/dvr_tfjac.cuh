@@ -94,22 +94,36 @@ __global__ void __launch_bounds__(kThreads, 4) k_tf_jacobian(const RayInputs in,
   for (int k = 0; k < NR; ++k) row[0][k] = row[1][k] = 0.f;
   constexpr int kNoBase = -0x40000000;
   int base = kNoBase;  // Texture: floor of the texture coordinate (-1 .. R); Linear: interval index
+  // one row of the window into the pixel's Jacobian slice (k = 0: row `base`, k = 1: row `base + 1`; Texture rows clamp)
+  auto flush_one = [&](int k) {
+    int r = base + k;
+    if constexpr (TF == kTfTexture) r = min(max(r, 0), in.R - 1);
+    const float* v = k ? row[1] : row[0];
+    add_colour(r, v[0]);
+    add4(s_dtf[r * ROW + 3], v + 1);
+    if constexpr (TF == kTfLinear) add4(s_dtf[r * ROW + 4], v + 5);
+  };
   auto flush = [&]() {
     if (base == kNoBase) return;
-    int r0 = base, r1 = base + 1;
-    if constexpr (TF == kTfTexture) {
-      r0 = min(max(r0, 0), in.R - 1);
-      r1 = min(max(r1, 0), in.R - 1);
-    }
+    flush_one(0);
+    flush_one(1);
 #pragma unroll
-    for (int k = 0; k < 2; ++k) {
-      const int r = k ? r1 : r0;
-      add_colour(r, row[k][0]);
-      add4(s_dtf[r * ROW + 3], &row[k][1]);
-      if constexpr (TF == kTfLinear) add4(s_dtf[r * ROW + 4], &row[k][5]);
+    for (int e = 0; e < NR; ++e) row[0][e] = row[1][e] = 0.f;
+  };
+  // the ray moves to another row pair: usually the neighbouring one, then one row of the window stays
+  auto move_window = [&](int key) {
+    if (key == base + 1) {
+      flush_one(0);
 #pragma unroll
-      for (int e = 0; e < NR; ++e) row[k][e] = 0.f;
+      for (int e = 0; e < NR; ++e) { row[0][e] = row[1][e]; row[1][e] = 0.f; }
+    } else if (key == base - 1) {
+      flush_one(1);
+#pragma unroll
+      for (int e = 0; e < NR; ++e) { row[1][e] = row[0][e]; row[0][e] = 0.f; }
+    } else {
+      flush();
     }
+    base = key;
   };
 
   Sampler<FILTER, false> smp;
@@ -122,21 +136,19 @@ __global__ void __launch_bounds__(kThreads, 4) k_tf_jacobian(const RayInputs in,
     const float t = sample_t(ray, f);
     return ga.exactPos ? sample_pos<true>(ray, t) : sample_pos<false>(ray, t);
   };
-  [[maybe_unused]] f3 pNext = {0.f, 0.f, 0.f};
-  [[maybe_unused]] unsigned qn = 0u;
   if constexpr (LOOKAHEAD) {
     if (n > 0) {
-      pNext = position(0.f);
-      smp.lookahead(in, pNext.x, pNext.y, pNext.z, qn);
+      const f3 p = position(0.f);
+      smp.lookahead_f(in, p.x, p.y, p.z);
     }
   }
   for (int i = 0; i < n; ++i, fi += 1.0f) {
     float density;
     if constexpr (LOOKAHEAD) {
-      density = smp.interp(pNext.x, pNext.y, pNext.z);
+      density = smp.interp_f();
       if (i + 1 < n) {  // the next sample's cell loads run under this sample's arithmetic (Sampler::lookahead)
-        pNext = position(fi + 1.0f);
-        smp.lookahead(in, pNext.x, pNext.y, pNext.z, qn);
+        const f3 p = position(fi + 1.0f);
+        smp.lookahead_f(in, p.x, p.y, p.z);
       }
     } else {
       const f3 p = position(fi);
@@ -218,10 +230,7 @@ __global__ void __launch_bounds__(kThreads, 4) k_tf_jacobian(const RayInputs in,
         const f4 v0 = lds4(s_tf + 8 * key), v1 = lds4(s_tf + 8 * (key + 1));
         dv = {v1.x - v0.x, v1.y - v0.y, v1.z - v0.z, v1.w - v0.w};
       }
-      if (key != base) {
-        flush();
-        base = key;
-      }
+      if (key != base) move_window(key);
       const float w0 = 1.f - w1;
       row[0][0] = fmaf(w0, q, row[0][0]);
       row[1][0] = fmaf(w1, q, row[1][0]);

@@ -294,7 +294,10 @@ typedef struct DvrCallOptions {
                                         D, csrc/dvr_tfjac.cuh; Gaussian tables of more than 28 rows: ceil(D / 8)
                                         slot-major passes), 1 always the slot-major passes (the reference's scheme in
                                         chunks; kept for A/B measurements). Read only when struct_size covers it */
-  int32_t reserved0;
+  int32_t adjoint_march_zero_rays;   /* adjoint: 0 (default) a ray whose adjoint colour is zero in all four channels is
+                                        not marched (its contributions are exact zeros: converged / masked pixels of
+                                        a reconstruction); 1 marches every ray like the reference does (same results;
+                                        for like-for-like timings) */
 } DvrCallOptions;
 
 DVR_API void dvr_call_options_init(DvrCallOptions* options); /* the defaults: -1, 0, 0, 0, NULL, 0 */

@@ -126,6 +126,17 @@ def test_rays_with_zero_adjoint_colour_are_skipped_without_changing_results(orac
     got = run_case(oracles, sc, adj_color_mask=mask)
     assert not got["adj_step_size"][:, :, : sc.W // 2].any()
     assert np.abs(got["adj_volume"]).max() > 0
+    # DvrCallOptions::adjoint_march_zero_rays = 1 marches them like the reference does: same results
+    want_c, want_t = scenes.np_forward(oracles[0], sc)
+    adj_color = np.random.RandomState(7).randn(*want_c.shape).astype(np.float32)
+    adj_color = adj_color * mask(adj_color)
+    all_rays = gr.adjoint(sc, want_c, want_t, adj_color, volume=True, step=True, camera=True, tf=True,
+                          options=capi.make_call_options(adjoint_march_zero_rays=True))
+    for k in got:
+        if k in ("adj_volume", "adj_tf"):
+            assert scenes.rel_l2(all_rays[k], got[k]) <= 2e-6, k
+        else:
+            assert np.array_equal(all_rays[k], got[k]), k
 
 
 def test_consistency_scenes_of_the_reference(oracles):
