@@ -428,7 +428,7 @@ enum : int { kRayNone = 0, kRayStep = 1, kRayCam = 2 };
 #ifndef DVR_ADJ_CTAS_1
 #define DVR_ADJ_CTAS_1 6   // ray gradients + one of the two: <= 80 registers
 #endif
-template <int TF, bool HAS_VOL, int TFACC, int RAY>
+template <int FILTER, int TF, bool HAS_VOL, int TFACC, int RAY>
 constexpr int adjoint_min_ctas() {
   if (RAY == kRayNone) return 1;
   // register accumulators of a Gaussian table (up to kRegRows x 6 floats of state): <= 128 registers
@@ -440,7 +440,7 @@ constexpr int adjoint_min_ctas() {
 }
 
 template <int FILTER, int TF, int BLEND, bool HAS_VOL, int TFACC, int RAY>
-__global__ void __launch_bounds__(kThreads, adjoint_min_ctas<TF, HAS_VOL, TFACC, RAY>()) k_adjoint(const RayInputs in,
+__global__ void __launch_bounds__(kThreads, adjoint_min_ctas<FILTER, TF, HAS_VOL, TFACC, RAY>()) k_adjoint(const RayInputs in,
                                                                                              const AdjointArgs aa) {
   constexpr bool HAS_RAY = RAY != kRayNone;
   extern __shared__ __align__(16) float smem[];
@@ -472,8 +472,8 @@ __global__ void __launch_bounds__(kThreads, adjoint_min_ctas<TF, HAS_VOL, TFACC,
     int n = __ldg(aa.term + b * aa.tB + y * aa.tY + x * aa.tX);
     // A ray whose adjoint colour is zero in all four channels contributes exact zeros to every output (converged or
     // masked pixels of a reconstruction): skip its march. The per-ray outputs below are still written (as zeros).
-    if (!aa.marchZeroRays && ((__float_as_uint(adjAcc.x) | __float_as_uint(adjAcc.y) | __float_as_uint(adjAcc.z) |
-                               __float_as_uint(adjAcc.w)) & 0x7fffffffu) == 0u)
+    if ((((__float_as_uint(adjAcc.x) | __float_as_uint(adjAcc.y) | __float_as_uint(adjAcc.z) | __float_as_uint(adjAcc.w)) &
+          0x7fffffffu) | unsigned(aa.marchZeroRays)) == 0u)
       n = 0;
     float adjStep = 0.f;
     f3 adjStart = {0.f, 0.f, 0.f}, adjDir = {0.f, 0.f, 0.f};
