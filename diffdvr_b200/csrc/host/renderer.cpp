@@ -172,7 +172,7 @@ void* current_stream(const torch::Device& dev) { return c10::cuda::getCurrentCUD
 // ---- host-layer options and the volume cache --------------------------------------------------------------------
 // The C-ABI is reentrant (options travel per call); this class is, like the reference's, a static facade with
 // process-wide settings (Renderer::setCudaSyncMode & co), so its defaults live here and are passed per call.
-std::atomic<int> g_compat_stepsize{0}, g_volume_layout{-1}, g_volume_cache{1}, g_forward_mode_tf{0};
+std::atomic<int> g_compat_stepsize{0}, g_volume_layout{-1}, g_volume_cache{1}, g_forward_mode_tf{0}, g_march_zero_rays{0};
 
 // One workspace per device, keyed on the volume TENSOR: (data_ptr, sizes, strides) are checked by the library,
 // the contents by torch's version counter (every in-place operation bumps it). The cache holds a handle of the
@@ -198,6 +198,7 @@ void fill_options(CallOptions& c, const RendererInputsHost& in, const torch::Dev
   c.o.volume_layout = g_volume_layout.load();
   c.o.compat_stepsize_overwrite = g_compat_stepsize.load();
   c.o.forward_mode_tf = g_forward_mode_tf.load();
+  c.o.adjoint_march_zero_rays = g_march_zero_rays.load();
   if (!g_volume_cache.load() || c.o.volume_layout == 0 || in.volumeFilterMode != kernel::FilterTrilinear) return;
   const int d = dev.index();
   if (d < 0 || d >= kMaxDevices) return;
@@ -279,6 +280,7 @@ void Renderer::setOption(const std::string& name, int value) {
     g_forward_mode_tf = value;
     return;
   }
+  if (name == "adjoint_march_zero_rays") { g_march_zero_rays = value != 0; return; }
   if (name == "volume_cache") {
     g_volume_cache = value != 0;
     if (!value) drop_volume_caches();
@@ -291,6 +293,7 @@ int Renderer::getOption(const std::string& name) {
   if (name == "volume_layout") return g_volume_layout.load();
   if (name == "volume_cache") return g_volume_cache.load();
   if (name == "forward_mode_tf") return g_forward_mode_tf.load();
+  if (name == "adjoint_march_zero_rays") return g_march_zero_rays.load();
   int32_t v = 0;
   raise_on_error(dvr_get_option(name.c_str(), &v));
   return v;

@@ -300,7 +300,7 @@ typedef struct DvrCallOptions {
                                         for like-for-like timings) */
 } DvrCallOptions;
 
-DVR_API void dvr_call_options_init(DvrCallOptions* options); /* the defaults: -1, 0, 0, 0, NULL, 0 */
+DVR_API void dvr_call_options_init(DvrCallOptions* options); /* the defaults: -1, 0, 0, 0, NULL, 0, 0 */
 
 DVR_API DvrWorkspace* dvr_workspace_create(void);            /* on the current device; NULL on failure */
 DVR_API void dvr_workspace_destroy(DvrWorkspace* ws);        /* frees its device buffers (synchronises) */
