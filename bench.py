@@ -66,6 +66,9 @@ def parse_args():
                    help="adjoint: let the library skip the rays whose adjoint colour is zero in all channels (its default: "
                         "their contributions are exact zeros). The bench marches every ray unless this is given, like the "
                         "reference arm does, so that both arms do the same work")
+    p.add_argument("--no-overlap", action="store_true",
+                   help="one stream: forward and adjoint launches strictly one after the other (default: the forward "
+                        "pass of the next launch runs on a second stream under the adjoint pass of the current one)")
     p.add_argument("--no-workspace", action="store_true",
                    help="per-call QUAD scratch (copy rebuilt, gradient scratch zeroed and folded on every call)")
     return p.parse_args()
@@ -361,7 +364,7 @@ def run_ours(a):
     adj_volume = torch.zeros_like(volume) if has_vol else None
     adj_tf = torch.zeros_like(tf_dev) if has_tf else None
     keep_images = w.res * w.res * w.batch * len(launches) <= 64 * 512 * 512   # C5: one colour buffer is reused
-    nbuf = len(launches) if keep_images else 1
+    nbuf = len(launches) if keep_images else (1 if a.no_overlap else min(2, len(launches)))
     colors = [torch.empty(min(w.batch, len(my_views)), H, W, 4, device=dev) for _ in range(nbuf)]
     terms = [torch.empty(min(w.batch, len(my_views)), H, W, dtype=torch.int32, device=dev) for _ in range(nbuf)]
     adj_steps = torch.zeros(min(w.batch, len(my_views)), H, W, device=dev) if has_step else None
@@ -378,9 +381,17 @@ def run_ours(a):
         per_ray_host = (torch.empty(len(my_views), H, W, 3).pin_memory(), torch.empty(len(my_views), H, W, 3).pin_memory())
     image_host = torch.empty(len(my_views), H, W, 4).pin_memory() if not w.adjoint and not fwd_mode else None
 
+    # Two-stream schedule for the gradient steps: the forward pass of launch k+1 does not depend on the adjoint pass
+    # of launch k (the volume changes once per step), so it runs on a second stream and fills the SMs the adjoint's
+    # last wave leaves idle. Per-launch kernel durations are measured in a separate single-stream pass (record=True).
+    overlap_ok = bool(w.adjoint) and not fwd_mode and not a.no_overlap and ws is not None
+    side_f = torch.cuda.Stream(device=dev) if overlap_ok else None
+    side_a = torch.cuda.Stream(device=dev) if overlap_ok else None
+
     def step_fn(e2e: bool, record: bool):
         """One gradient step over this rank's views. Returns the loss (tensor; float in e2e mode)."""
         vol, tf, cams = volume, tf_dev, cam_dev
+        overlap = overlap_ok and not record
         if e2e:  # host -> device copies of this step's inputs (pinned memory); the volume arrives in per-rank slices
             my = vol_slice_host.to(dev, non_blocking=True)
             if world == 1:
@@ -402,10 +413,41 @@ def run_ours(a):
         if has_tf:
             adj_tf.zero_()
         loss = torch.zeros((), device=dev)
+        cur = torch.cuda.current_stream()
+        if overlap:
+            side_f.wait_stream(cur)
+            side_a.wait_stream(cur)
+            adj_done = []
         for k, idx in enumerate(launches):
             nb = len(idx)
             color, term = colors[k % nbuf][:nb], terms[k % nbuf][:nb]
             inp = inputs(vol, tf, cams[k], idx)
+            if overlap:
+                # forward on its own stream (after the adjoint that last read this colour buffer), loss + adjoint on the other
+                if k >= nbuf:
+                    side_f.wait_event(adj_done[k - nbuf])
+                lib.render_forward(inp, color, term, side_f.cuda_stream, opts)
+                fwd_done = torch.cuda.Event()
+                fwd_done.record(side_f)
+                side_a.wait_event(fwd_done)
+                with torch.cuda.stream(side_a):
+                    if w.name == "C4":
+                        diff = color[..., 3] - targets[k]
+                        loss += diff.abs().sum() / n_pix_total
+                        adj_color = torch.zeros_like(color)
+                        adj_color[..., 3] = torch.sign(diff) / n_pix_total
+                    else:
+                        diff = color - targets[k]
+                        loss += diff.abs().sum() / n_pix_total
+                        adj_color = torch.sign(diff) / n_pix_total
+                    adj = capi.make_adjoint_outputs(adj_volume=adj_volume, adj_tf=adj_tf,
+                                                    adj_step_size=adj_steps[:nb] if has_step else None,
+                                                    tf_delayed_accumulation=w.delayed_tf)
+                    lib.render_adjoint(inp, color, term, adj_color, adj, side_a.cuda_stream, opts)
+                    done = torch.cuda.Event()
+                    done.record(side_a)
+                    adj_done.append(done)
+                continue
             if record:
                 e0, e1, e1b, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(4))
                 e0.record()
@@ -447,6 +489,9 @@ def run_ours(a):
                 e2.record()
                 fwd_ev.append((e0, e1))
                 adj_ev.append((e1b, e2))
+        if overlap:
+            cur.wait_stream(side_f)
+            cur.wait_stream(side_a)
         if has_vol and ws is not None:
             ws.end_volume_gradient(adj_volume, stream)
         grad_slice = None
@@ -499,9 +544,11 @@ def run_ours(a):
     torch.cuda.synchronize()
     stats0 = {k: lib.stat(k) for k in ("launches", "quad_builds", "quad_reuses", "quad_fallbacks", "folds")}
     with ClockSampler(local_rank) as clocks:
-        ms_step = timed(False, a.steps, True)
+        ms_step = timed(False, a.steps, not overlap_ok)   # with the two-stream schedule the kernels are timed below
         stats1 = {k: lib.stat(k) for k in stats0}
         ms_e2e = timed(True, a.steps, False)
+    if overlap_ok:   # per-launch kernel durations: one single-stream pass, outside the timed regions
+        timed(False, 1, True)
     torch.cuda.synchronize()
     per_step = {k: (stats1[k] - stats0[k]) / float(a.steps) for k in stats0}
 
@@ -616,7 +663,8 @@ def run_ours(a):
                    sharding="views round-robin over ranks; device-timed value: volume replicated, gradient all-reduce(sum); "
                             "e2e: each rank owns 1/N of the volume and of its gradient on the host (H2D of the slice, "
                             "all-gather over NVLink, reduce-scatter, D2H of the slice)",
-                   workspace=ws is not None)
+                   workspace=ws is not None,
+                   streams="two: forward(k+1) on a second stream under adjoint(k)" if overlap_ok else "one")
         out = {
             "metric": METRICS[w.name], "value": w.views / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": a.steps, "warmup": warm, "ms_per_step": ms_step, "higher_is_better": True,
