@@ -90,6 +90,7 @@ class DvrAdjointOutputs(ctypes.Structure):
 
 
 ABI_VERSION = 3  # include/dvr_b200.h DVR_ABI_VERSION
+NOALLOC_MAX_QUADS = 129 * 128 * 128  # include/dvr_b200.h DVR_NOALLOC_MAX_QUADS
 
 
 class DvrCallOptions(ctypes.Structure):
@@ -451,6 +452,8 @@ class ProductLibrary(Library):
                   L.dvr_workspace_end_volume_gradient):
             f.restype = ctypes.c_int
             f.argtypes = [ctypes.c_void_p, P(DvrTensor), ctypes.c_void_p]
+        L.dvr_render_forward_noalloc.restype = ctypes.c_int
+        L.dvr_render_forward_noalloc.argtypes = [P(DvrInputs), P(DvrOutputs), ctypes.c_void_p]
         L.dvr_trim_scratch.restype = ctypes.c_int
         L.dvr_trim_scratch.argtypes = []
         L.dvr_get_stat.restype = ctypes.c_int
@@ -487,6 +490,13 @@ class ProductLibrary(Library):
         self._validate(inputs, [("color", color, "float32"), ("terminationIndex", termination_index, "int32")])
         ci, co = inputs.to_c(), make_outputs(color, termination_index)
         self._check(self.lib.dvr_render_forward_ex(ci, co, options, self._stream(stream)))
+
+    def render_forward_noalloc(self, inputs: Inputs, color, termination_index, stream=None):
+        """dvr_render_forward_noalloc: the forward pass with its QUAD copy in the library's static device array
+        (NOALLOC_MAX_QUADS entries); allocates nothing; calls that overlap on the GPU race on that array."""
+        self._validate(inputs, [("color", color, "float32"), ("terminationIndex", termination_index, "int32")])
+        ci, co = inputs.to_c(), make_outputs(color, termination_index)
+        self._check(self.lib.dvr_render_forward_noalloc(ci, co, self._stream(stream)))
 
     def render_forward_gradients(self, inputs: Inputs, settings: DvrForwardDifferencesSettings, color,
                                  termination_index, gradients_out, stream=None, options: DvrCallOptions = None):

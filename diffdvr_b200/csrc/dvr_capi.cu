@@ -620,6 +620,34 @@ cudaError_t launch_forward_gradients(int filter, int tf, int blend, int chunk, b
 
 }  // namespace dvr
 
+// ---- dvr_render_forward_noalloc: the QUAD copy in static device memory -----------------------------------------
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc): the QUAD copy
+// of the volume lives in this file-scope array instead of pool / workspace memory. Every GPU that loads the library
+// holds the array (DVR_NOALLOC_MAX_QUADS x 16 bytes = 33.8 MB) until the process exits. The name is a host-side
+// stand-in in host code: the device address comes from cudaGetSymbolAddress, once per device, with that device current.
+static __device__ __align__(256) float4 g_noalloc_quads[DVR_NOALLOC_MAX_QUADS];
+
+namespace {
+
+float4* g_noalloc_ptr[kMaxDevices] = {};
+std::mutex g_noalloc_mutex;
+
+float4* noalloc_quads() {
+  int dev = 0;
+  cuda_check(cudaGetDevice(&dev), "dvr_render_forward_noalloc: cudaGetDevice");
+  if (dev < 0 || dev >= kMaxDevices) fail(DVR_ERR_UNSUPPORTED, "dvr_render_forward_noalloc: device %d outside [0, %d)", dev, kMaxDevices);
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_ptr[dev]) {
+    void* p = nullptr;
+    cuda_check(cudaGetSymbolAddress(&p, g_noalloc_quads), "dvr_render_forward_noalloc: cudaGetSymbolAddress(g_noalloc_quads)");
+    if (!p) fail(DVR_ERR_CUDA, "dvr_render_forward_noalloc: cudaGetSymbolAddress returned NULL");
+    g_noalloc_ptr[dev] = static_cast<float4*>(p);
+  }
+  return g_noalloc_ptr[dev];
+}
+
+}  // namespace
+
 // ================================================================================================
 extern "C" {
 
@@ -658,6 +686,44 @@ int dvr_render_forward_ex(const DvrInputs* inputs, const DvrOutputs* outputs, co
     after_launch(launch_forward(filter, inputs->tf_mode, inputs->blend_mode, c.ri, fo,
                                 tile_grid(c), smem, s),
                  "dvr_render_forward", s);
+  });
+}
+
+// Forward render that allocates nothing (include/dvr_b200.h): same checks, same kernels as dvr_render_forward_ex with
+// volume_layout = 1, the QUAD copy built into g_noalloc_quads. No cudaMalloc / cudaFree / pool call on this path.
+int dvr_render_forward_noalloc(const DvrInputs* inputs, const DvrOutputs* outputs, void* stream) {
+  return guarded([&] {
+    if (!inputs || !outputs) fail(DVR_ERR_INVALID_ARGUMENT, "NULL argument");
+    t_call_sync = 0;
+    Checked c;
+    check_inputs(*inputs, c);
+    const ForwardOutputs fo = check_outputs(*outputs, c);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (inputs->tf_mode == DVR_TF_PRESHADED) {  // no scratch in this kernel
+      after_launch(launch_forward_preshaded(inputs->blend_mode, c.ri, fo, tile_grid(c), s), "dvr_render_forward_noalloc", s);
+      return;
+    }
+    const size_t smem = check_smem(size_t(c.ri.R) * tf_row(inputs->tf_mode) * sizeof(float));
+    int filter = inputs->volume_filter_mode;
+    if (filter == DVR_FILTER_TRILINEAR && quad_eligible(c)) {  // (volumes thinner than 2 voxels: in place, no scratch)
+      const long long quadsPer = quad_count(c.X, c.Y, c.Z);
+      const int nb = c.ri.volB == 0 ? 1 : c.B;
+      if (quadsPer * nb > (long long)DVR_NOALLOC_MAX_QUADS)
+        fail(DVR_ERR_UNSUPPORTED,
+             "dvr_render_forward_noalloc: the QUAD copy of %d volume(s) of %d x %d x %d needs %lld entries ((X + 1) * Y * Z "
+             "each), the static scratch holds DVR_NOALLOC_MAX_QUADS = %lld (one 128^3 volume); use dvr_render_forward_ex",
+             nb, c.X, c.Y, c.Z, quadsPer * nb, (long long)DVR_NOALLOC_MAX_QUADS);
+      float4* quads = noalloc_quads();
+      // the build kernel overwrites every entry the march reads ((X + 1) * Y * Z per volume): nothing to clear
+      after_launch(launch_build_quads(c.ri, nb, quads, s), "dvr_build_quads", s);
+      g_quad_builds.fetch_add(1, std::memory_order_relaxed);
+      c.ri.quads = quads;
+      c.ri.quadB = nb == 1 ? 0 : quadsPer;
+      set_quad_indexing(c.ri);
+      filter = kFilterTrilinearQuad;
+    }
+    after_launch(launch_forward(filter, inputs->tf_mode, inputs->blend_mode, c.ri, fo, tile_grid(c), smem, s),
+                 "dvr_render_forward_noalloc", s);
   });
 }
 

@@ -325,6 +325,22 @@ DVR_API int dvr_render_adjoint_ex(const DvrInputs* inputs, const DvrOutputs* out
                                   const DvrTensor* adj_color, const DvrAdjointOutputs* adj_outputs,
                                   const DvrCallOptions* options, void* stream);
 
+/* Forward render that ALLOCATES NOTHING: dvr_render_forward with the QUAD copy of the volume (the scratch the trilinear
+ * marcher reads, see above) in a static device array of the library instead of pool / workspace memory. No counterpart
+ * in the reference; added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it). No cudaMalloc, cudaFree, memory-pool or other
+ * allocating call is made. Same inputs, outputs, checks, kernels and results as dvr_render_forward_ex with
+ * volume_layout = 1.
+ *   Limit : B_vol * (X + 1) * Y * Z <= DVR_NOALLOC_MAX_QUADS (B_vol = 1 for a volume shared by the batch), i.e. one
+ *           volume of up to 128^3; larger volumes return DVR_ERR_UNSUPPORTED with a message (no fallback). The array
+ *           (33.8 MB) is held by every GPU that loads the library, until the process exits.
+ *   Shared: every call on a device uses the same array. Calls that may overlap on the GPU (different streams without
+ *           an ordering between them) RACE on it; order them. The array keeps the last call's contents; the build
+ *           kernel of each call overwrites every entry its march reads, so nothing has to start at zero.
+ *   Nearest / preshaded filters and volumes thinner than 2 voxels run their usual kernels, which use no scratch. */
+#define DVR_NOALLOC_MAX_QUADS 2113536 /* 129 * 128 * 128 float4 entries */
+DVR_API int dvr_render_forward_noalloc(const DvrInputs* inputs, const DvrOutputs* outputs, void* stream);
+
 /* Releases the pages the library's private scratch pool holds on the current device. */
 DVR_API int dvr_trim_scratch(void);
 
