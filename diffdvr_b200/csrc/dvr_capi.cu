@@ -519,10 +519,19 @@ bool quad_eligible(const Checked& c) {
 long long quad_count(int X, int Y, int Z) { return ((long long)X + 1) * Y * Z; }
 
 void set_quad_indexing(RayInputs& r) {
+#if DVR_QUAD_XINNER
+  const unsigned SZ = unsigned(r.X) + 1u, SY = SZ * unsigned(r.Z);
+  r.quadYZ = SY;
+  r.quadSZ = SZ;
+  r.quadBias = unsigned(kTwo23Bits) * (SY + SZ + 1u);
+  r.quadMax = SY * unsigned(r.Y) - 2u;
+#else
   const unsigned YZ = unsigned(r.Y) * unsigned(r.Z);
   r.quadYZ = YZ;
+  r.quadSZ = 1u;
   r.quadBias = unsigned(kTwo23Bits) * (YZ + unsigned(r.Z) + 1u);
   r.quadMax = unsigned(r.X) * YZ - 1u;
+#endif
 }
 
 // returns the filter id to dispatch on (kFilterTrilinearQuad if a QUAD copy of the volume serves this call)

@@ -477,16 +477,23 @@ __global__ void __launch_bounds__(kThreads, adjoint_min_ctas<FILTER, TF, HAS_VOL
       n = 0;
     float adjStep = 0.f;
     f3 adjStart = {0.f, 0.f, 0.f}, adjDir = {0.f, 0.f, 0.f};
-    Sampler<FILTER, HAS_VOL> smp;
+    Sampler<FILTER, HAS_VOL, DVR_BRANCHFREE_ADJ || (DVR_BRANCHFREE_NORAY && !HAS_RAY)> smp;
     if constexpr (FILTER == kFilterTrilinearQuad && HAS_VOL)
       smp.init(in, b, reinterpret_cast<float*>(aa.gradQuads), aa.gradQuadB * 4);
     else
       smp.init(in, b, aa.adjVolume, aa.avB);
     // terminationIndex-1 was the last sample that contributed (renderer_kernels.cuh:374-376)
     float fi = float(n - 1);
+    // Beer-Lambert: the loop carries the transmittance in acc.w (blend_adjoint_T). Not in the instances that differentiate
+    // the ray position: their config-size gradients sit within 1e-4 of the fp32 reference build only because the
+    // inversion rounds like the reference's (with T they move to 8e-4 from it -- and from 8.6e-4 to 3.3e-4 from the
+    // reference's fp64 build, profiles/r02_xinner.md; the parity gate is the fp32 build)
+    constexpr bool TMODE = BLEND == kBlendBeer && DVR_BLEND_T && RAY != kRayCam;
+    if constexpr (TMODE) acc.w = 1.f - acc.w;
     // Identity TF: ray constants of blend_adjoint_grey
     [[maybe_unused]] const float idSa = s_tf[0], idSc = s_tf[1];
     [[maybe_unused]] const float idKS = (adjAcc.x + adjAcc.y + adjAcc.z) * idSc;
+    [[maybe_unused]] const float idStepSa = ray.step * idSa;
     // Without position derivatives the sample position needs no t: p_i = (ps + tmin pd) + i (step pd), two hoisted
     // vectors and one FMA per axis (the forward pass rounds tmin + i step first; the positions agree to an ulp, which
     // moves the reconstructed densities by ~1e-6 relative, far inside the gradient tolerance).
@@ -541,14 +548,17 @@ __global__ void __launch_bounds__(kThreads, adjoint_min_ctas<FILTER, TF, HAS_VOL
         }
       } else {
         p = position(fi, t);
-        density = smp.fetch(in, &aa, p.x, p.y, p.z);
+        if constexpr (FILTER == kFilterTrilinearQuad && HAS_VOL && DVR_PRED_ADJ) density = smp.fetch_pred(in, p.x, p.y, p.z);
+        else density = smp.fetch(in, &aa, p.x, p.y, p.z);
       }
       float adjDensity, adjStepBlend;
       if constexpr (TF == kTfIdentity) {
         // r = g = b (renderer_tf.cuh:62-104): one colour lane through the blend inversion and the TF adjoint
         const float dc = fmaxf(0.f, fminf(density, 1.f));
         float ak, adjAlphaE;
-        const float adjDc = blend_adjoint_grey<BLEND>(acc.w, adjAcc.w, dc, idKS, idSa, ray.step, ak, adjAlphaE);
+        float adjDc;
+        if constexpr (TMODE) adjDc = blend_adjoint_grey_T(acc.w, adjAcc.w, dc, idKS, idSa, ray.step, idStepSa, ak, adjAlphaE);
+        else adjDc = blend_adjoint_grey<BLEND>(acc.w, adjAcc.w, dc, idKS, idSa, ray.step, ak, adjAlphaE);
         adjStepBlend = adjAlphaE * (dc * idSa);
         if constexpr (TFACC == kTfAccReg) {
           tfg.g[0] = fmaf(adjAlphaE * ray.step, dc, tfg.g[0]);                       // d/d scaleAbsorption
@@ -562,7 +572,8 @@ __global__ void __launch_bounds__(kThreads, adjoint_min_ctas<FILTER, TF, HAS_VOL
         TfCache<TF> tfCache;
         const f4 cur = tf_eval_cached<TF>(s_tf, in.R, density, tfCache);
         f4 adjCur;
-        blend_adjoint<BLEND, false>(acc, adjAcc, cur, ray.step, adjCur, adjStepBlend);
+        if constexpr (TMODE) blend_adjoint_T(acc.w, adjAcc, cur, ray.step, adjCur, adjStepBlend);
+        else blend_adjoint<BLEND, false>(acc, adjAcc, cur, ray.step, adjCur, adjStepBlend);
         adjDensity = tf_adjoint<TF, TFACC>(s_tf, in.R, density, adjCur, tfg, tfCache);
       }
       f3 g;

@@ -144,14 +144,125 @@ __global__ void __launch_bounds__(256) k_fold_quads(const RayInputs in, const Ad
   }
 }
 
+// ---- the same two passes for the x-innermost layout Q[b][y][z][x] (DVR_QUAD_XINNER) ----------------------------------
+// Both are transposes: the volume and adj_volume are z-fastest (contiguous torch tensors; any strides are handled, those
+// are the coalesced ones), the quads x-fastest. One CTA of 256 threads owns a 32 (x) x 32 (z) tile of one y row and
+// goes through shared memory, so both sides move whole lines.
+constexpr int kTile = 32;
+
+__global__ void __launch_bounds__(256) k_build_quads_xinner(const RayInputs in, float4* quads, unsigned tilesX,
+                                                            unsigned tilesZ) {
+  __shared__ float t[2][kTile][kTile + 1];  // [row y / y'][x][z0 .. z0 + 32]; odd pitch: conflict-free both ways
+  const unsigned X = unsigned(in.X), Y = unsigned(in.Y), Z = unsigned(in.Z);
+  unsigned blk = blockIdx.x;
+  const unsigned tx = blk % tilesX; blk /= tilesX;
+  const unsigned tz = blk % tilesZ;
+  const unsigned y = blk / tilesZ;
+  const unsigned x0 = tx * kTile, z0 = tz * kTile;
+  const unsigned y1 = min(y + 1, Y - 1);
+  const int b = blockIdx.z;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const float* v = in.volume + b * in.volB;
+  // load: lanes along z (33 values per row: z0 .. z0 + 32, clamped to Z - 1), rows = (y | y') x 32 x-values (slice X
+  // duplicates slice X - 1)
+  for (unsigned r = warp; r < 2 * kTile; r += 8) {
+    const unsigned xs = min(x0 + (r & (kTile - 1)), X - 1), yy = r < kTile ? y : y1;
+    const float* row = v + (long long)xs * in.sx + (long long)yy * in.sy;
+    t[r >> 5][r & (kTile - 1)][lane] = __ldg(row + (long long)min(z0 + lane, Z - 1) * in.sz);
+    if (lane == 0) t[r >> 5][r & (kTile - 1)][kTile] = __ldg(row + (long long)min(z0 + kTile, Z - 1) * in.sz);
+  }
+  __syncthreads();
+  // store: lanes along x
+  const unsigned x = x0 + lane;
+  if (x > X) return;
+  float4* out = quads + (size_t)b * ((size_t)(X + 1) * Y * Z) + ((size_t)y * Z) * (X + 1) + x;
+  for (unsigned zl = warp; zl < kTile; zl += 8) {
+    const unsigned z = z0 + zl;
+    if (z >= Z) break;
+    out[(size_t)z * (X + 1)] = make_float4(t[0][lane][zl], t[0][lane][zl + 1], t[1][lane][zl], t[1][lane][zl + 1]);
+  }
+}
+
+// same sums in the same order as k_fold_quads (bit-identical results for the same scratch contents)
+__global__ void __launch_bounds__(256) k_fold_quads_xinner(const RayInputs in, const AdjointArgs aa, unsigned tilesX,
+                                                           unsigned tilesZ) {
+  __shared__ float t[kTile][kTile + 1];  // [z][x]
+  const unsigned X = unsigned(in.X), Y = unsigned(in.Y), Z = unsigned(in.Z);
+  unsigned blk = blockIdx.x;
+  const unsigned tx = blk % tilesX; blk /= tilesX;
+  const unsigned tz = blk % tilesZ;
+  const unsigned y = blk / tilesZ;
+  const unsigned x0 = tx * kTile, z0 = tz * kTile;
+  const int b = blockIdx.z;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned SZ = X + 1, SY = SZ * Z;
+  const float4* g = aa.gradQuads + (size_t)b * aa.gradQuadB;
+  const bool yl = y == Y - 1;
+  // gather: lanes along x (coalesced 16-byte reads)
+  for (unsigned zl = warp; zl < kTile; zl += 8) {
+    const unsigned z = z0 + zl, x = x0 + lane;
+    float s = 0.f;
+    if (z < Z && x < X) {
+      const bool zlast = z == Z - 1;
+      auto gather = [&](size_t j) {
+        const float4 q = g[j];
+        float a = q.x;
+        if (zlast) a += q.y;
+        if (yl) a += q.z;
+        if (zlast && yl) a += q.w;
+        if (z > 0) {
+          const float4 r = g[j - SZ];
+          a += r.y;
+          if (yl) a += r.w;
+        }
+        if (y > 0) {
+          const float4 r = g[j - SY];
+          a += r.z;
+          if (zlast) a += r.w;
+        }
+        if (y > 0 && z > 0) a += g[j - SY - SZ].w;
+        return a;
+      };
+      const size_t j = (size_t)y * SY + (size_t)z * SZ + x;
+      s = gather(j);
+      if (x == X - 1) s += gather(j + 1);
+    }
+    t[zl][lane] = s;
+  }
+  __syncthreads();
+  // scatter: lanes along z
+  const unsigned z = z0 + lane;
+  if (z >= Z) return;
+  for (unsigned xl = warp; xl < kTile; xl += 8) {
+    const unsigned x = x0 + xl;
+    if (x >= X) break;
+    const float s = t[lane][xl];
+    if (s != 0.f) {
+      float* p = aa.adjVolume + b * aa.avB + (long long)x * aa.avx + (long long)y * aa.avy + (long long)z * aa.avz;
+      *p += s;
+    }
+  }
+}
+
 cudaError_t launch_fold_quads(const RayInputs& in, const AdjointArgs& aa, int nb, cudaStream_t s) {
+#if DVR_QUAD_XINNER
+  const unsigned tilesX = (unsigned(in.X) + kTile - 1) / kTile, tilesZ = (unsigned(in.Z) + kTile - 1) / kTile;
+  return launch_kernel(k_fold_quads_xinner, dim3(tilesX * tilesZ * unsigned(in.Y), 1, nb), 256, 0, s, in, aa, tilesX, tilesZ);
+#else
   const unsigned n = unsigned(in.X) * unsigned(in.Y) * unsigned(in.Z);
   return launch_kernel(k_fold_quads, dim3((n + 255) / 256, 1, nb), 256, 0, s, in, aa);
+#endif
 }
 
 cudaError_t launch_build_quads(const RayInputs& in, int nb, float4* quads, cudaStream_t s) {
+#if DVR_QUAD_XINNER
+  const unsigned tilesX = (unsigned(in.X) + 1u + kTile - 1) / kTile, tilesZ = (unsigned(in.Z) + kTile - 1) / kTile;
+  return launch_kernel(k_build_quads_xinner, dim3(tilesX * tilesZ * unsigned(in.Y), 1, nb), 256, 0, s, in, quads, tilesX,
+                       tilesZ);
+#else
   const unsigned n = (unsigned(in.X) + 1u) * unsigned(in.Y) * unsigned(in.Z);
   return launch_kernel(k_build_quads, dim3((n + 255) / 256, 1, nb), 256, 0, s, in, quads);
+#endif
 }
 
 cudaError_t launch_count_cells(const RayInputs& in, const int* term, long long tB, long long tY, long long tX,

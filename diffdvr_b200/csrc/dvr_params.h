@@ -6,6 +6,13 @@
 #pragma once
 #include <stdint.h>
 
+// Layout of the QUAD buffers (RayInputs::quads, AdjointArgs::gradQuads): 0 = Q[x][y][z] (z innermost, the two quads of
+// a cell Y*Z entries apart), 1 = Q[y][z][x] (x innermost: the two quads of a cell are NEIGHBOURS -- one address, an
+// immediate +16 for the second access, and 7 of 8 cells have both quads in one 128-byte line)
+#ifndef DVR_QUAD_XINNER
+#define DVR_QUAD_XINNER 1
+#endif
+
 namespace dvr {
 
 // tile geometry: one warp = 8x4 pixels, one CTA = 2x2 warps = 16x8 pixels
@@ -42,6 +49,9 @@ struct RayInputs {
   // hoisted index arithmetic of the QUAD cell load: q = ux*quadYZ + uy*Z + uz - quadBias on the biased-float bit
   // patterns of the cell coordinates (dvr_device.cuh load_cell), clamped to quadMax = X*Y*Z - 1 as a safety net
   unsigned quadYZ, quadBias, quadMax;
+  // DVR_QUAD_XINNER layout Q[b][y][z][x] (x in [0, X], innermost): q = uy*quadYZ + uz*quadSZ + ux - quadBias with
+  // quadYZ = Z*(X+1) (the y stride), quadSZ = X+1, quadMax = (X+1)*Y*Z - 2; the x + 1 quad of a cell is q + 1
+  unsigned quadSZ;
   Strided1 boxMin, boxSize;          // p == nullptr -> use the *V value
   float boxMinV[3], boxSizeV[3];
   int cameraMode;

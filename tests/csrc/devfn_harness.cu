@@ -46,6 +46,26 @@ __global__ void k_blend_adjoint(int n, const float* x, const float* e, const flo
   accIn[4 * i] = acc.x; accIn[4 * i + 1] = acc.y; accIn[4 * i + 2] = acc.z; accIn[4 * i + 3] = acc.w;
 }
 
+// the transmittance form of the Beer-Lambert adjoint step the adjoint kernels use (blend_adjoint_T, DVR_BLEND_T): same
+// inputs / outputs; the colour channels of the reconstructed accumulator are not produced (the kernels never read them)
+__global__ void k_blend_adjoint_T(int n, const float* x, const float* e, const float* g, float* z, float* accIn) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float* v = x + 9 * i;
+  float T = 1.f - e[4 * i + 3];
+  f4 adjAcc = {g[4 * i], g[4 * i + 1], g[4 * i + 2], g[4 * i + 3]};
+  const f4 cur = {v[4], v[5], v[6], v[7]};
+  f4 adjCur;
+  float adjStep;
+  blend_adjoint_T(T, adjAcc, cur, v[8], adjCur, adjStep);
+  float* o = z + 9 * i;
+  o[0] = adjAcc.x; o[1] = adjAcc.y; o[2] = adjAcc.z; o[3] = adjAcc.w;
+  o[4] = adjCur.x; o[5] = adjCur.y; o[6] = adjCur.z; o[7] = adjCur.w;
+  o[8] = adjStep;
+  accIn[4 * i] = accIn[4 * i + 1] = accIn[4 * i + 2] = 0.f;
+  accIn[4 * i + 3] = 1.f - T;
+}
+
 RayInputs tf_inputs(const float* tf, int R, int C) {
   RayInputs in{};
   in.tf = {tf, 0, (long long)C, 1};
@@ -101,9 +121,17 @@ RayInputs volume_inputs(const float* volume, int X, int Y, int Z, const float4* 
   in.volume = volume;
   in.sx = Y * Z; in.sy = Z; in.sz = 1;
   in.quads = quads;
+#if DVR_QUAD_XINNER  // as set_quad_indexing() of dvr_capi.cu
+  in.quadSZ = unsigned(X) + 1u;
+  in.quadYZ = in.quadSZ * unsigned(Z);
+  in.quadBias = unsigned(kTwo23Bits) * (in.quadYZ + in.quadSZ + 1u);
+  in.quadMax = in.quadYZ * unsigned(Y) - 2u;
+#else
   in.quadYZ = unsigned(Y) * unsigned(Z);
+  in.quadSZ = 1u;
   in.quadBias = unsigned(kTwo23Bits) * (in.quadYZ + unsigned(Z) + 1u);
   in.quadMax = unsigned(X) * in.quadYZ - 1u;
+#endif
   return in;
 }
 
@@ -123,7 +151,7 @@ __global__ void k_interp_adjoint(const RayInputs in, const AdjointArgs aa, int n
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const long long N = FILTER == kFilterTrilinearQuad ? (long long)(in.X + 1) * in.Y * in.Z * 4 : (long long)in.X * in.Y * in.Z;
-  Sampler<FILTER, true> smp;
+  Sampler<FILTER, true, DVR_BRANCHFREE_NORAY != 0> smp;  // as the adjoint kernels without ray gradients
   smp.init(in, 0, adjVolume + i * N, 0);
   smp.fetch(in, &aa, pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]);
   const f3 ap = smp.template adjoint<true>(g[i]);
@@ -150,7 +178,8 @@ DEVFN_API int devfn_blend(int32_t mode, int32_t n, const float* x, float* out) {
 
 DEVFN_API int devfn_blend_adjoint(int32_t mode, int32_t n, const float* x, const float* e, const float* g, float* z,
                                   float* accIn) {
-  if (mode == kBlendBeer) k_blend_adjoint<kBlendBeer><<<blocks(n), 128>>>(n, x, e, g, z, accIn);
+  if (mode == 100) k_blend_adjoint_T<<<blocks(n), 128>>>(n, x, e, g, z, accIn);  // Beer-Lambert, transmittance form
+  else if (mode == kBlendBeer) k_blend_adjoint<kBlendBeer><<<blocks(n), 128>>>(n, x, e, g, z, accIn);
   else k_blend_adjoint<kBlendAlpha><<<blocks(n), 128>>>(n, x, e, g, z, accIn);
   return done();
 }
@@ -186,6 +215,9 @@ DEVFN_API int devfn_tf_adjoint(int32_t mode, int32_t R, int32_t C, const float* 
   }
   return done();
 }
+
+// layout of the QUAD buffers this build expects: 0 = [x][y][z] quads, 1 = [y][z][x] quads (DVR_QUAD_XINNER)
+DEVFN_API int devfn_quad_xinner() { return DVR_QUAD_XINNER; }
 
 // quads: nullptr = sample the linear volume in place; else the QUAD copy of it ((X+1)*Y*Z float4, dvr_misc.cu layout)
 DEVFN_API int devfn_interp(int32_t X, int32_t Y, int32_t Z, const float* volume, const float* quads, int32_t n,

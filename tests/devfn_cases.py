@@ -161,20 +161,33 @@ class DeviceFns:
         self._call("devfn_tf_adjoint", mode, t.shape[0], t.shape[1], t, len(d), d, g, adj_d, adj_tf, acc)
         return adj_d.cpu().numpy(), adj_tf.cpu().numpy()
 
+    def quads(self, volume):
+        """device QUAD copy in the layout the harness build expects ([x][y][z] quads, or [y][z][x] with DVR_QUAD_XINNER)"""
+        q = build_quads(np.asarray(volume, np.float32))
+        return self.dev(q.transpose(1, 2, 0, 3) if self.lib.devfn_quad_xinner() else q)
+
     def interp(self, volume, pos, quad=False):
         v, p = self.dev(volume), self.dev(pos)
-        q = self.dev(build_quads(np.asarray(volume, np.float32))) if quad else None
+        q = self.quads(volume) if quad else None
         out = self.zeros(len(p))
         self._call("devfn_interp", *v.shape, v, q, len(p), p, out)
         return out.cpu().numpy()
 
     def interp_adjoint(self, volume, pos, g, quad=False):
         v, p, g = self.dev(volume), self.dev(pos), self.dev(g)
-        q = self.dev(build_quads(np.asarray(volume, np.float32))) if quad else None
+        q = self.quads(volume) if quad else None
         adj_pos = self.zeros(len(p), 3)
-        adj_vol = self.zeros(len(p), v.shape[0] + 1, *v.shape[1:], 4) if quad else self.zeros(len(p), *v.shape)
+        xinner = bool(self.lib.devfn_quad_xinner())
+        if not quad:
+            adj_vol = self.zeros(len(p), *v.shape)
+        elif xinner:
+            adj_vol = self.zeros(len(p), v.shape[1], v.shape[2], v.shape[0] + 1, 4)
+        else:
+            adj_vol = self.zeros(len(p), v.shape[0] + 1, *v.shape[1:], 4)
         self._call("devfn_interp_adjoint", *v.shape, v, q, len(p), p, g, adj_pos, adj_vol)
         av = adj_vol.cpu().numpy()
+        if quad and xinner:
+            av = np.ascontiguousarray(av.transpose(0, 3, 1, 2, 4))
         return adj_pos.cpu().numpy(), (fold_quads(av).astype(np.float32) if quad else av)
 
 

@@ -53,6 +53,22 @@ def test_blending(mode):
         _close(acc_in[keep], wacc[keep], dict(rtol=1e-4, atol=1e-5), "reconstructed accumulator")
 
 
+def test_blending_transmittance_form():
+    """blend_adjoint_T (what the Beer-Lambert adjoint kernels call: the step on T = 1 - acc.w, no quotient) against the
+    oracles' blend adjoint (renderer_blending.cuh:63-98) on the same vectors; mode 100 of the harness"""
+    dev = dc.DeviceFns()
+    rng = np.random.RandomState(3)
+    x = np.concatenate([dc.blend_inputs(), rng.uniform(0.01, 0.99, (2000, 9))]).astype(np.float32)
+    for o in _oracles():
+        want = o.blend(capi.BLEND_BEER_LAMBERT, x)
+        g = rng.uniform(-1, 1, want.shape).astype(np.float32)
+        z, acc_in = dev.blend_adjoint(100, x, want, g)
+        wz, wacc = o.blend_adjoint(capi.BLEND_BEER_LAMBERT, x, want, g)
+        keep = want[:, 3] < 0.999
+        _close(z[keep], wz[keep], ADJ, "blend adjoint (transmittance form)")
+        _close(acc_in[keep, 3], wacc[keep, 3], dict(rtol=1e-4, atol=1e-5), "reconstructed alpha")
+
+
 @pytest.mark.parametrize("name", sorted(TF_MODES))
 def test_transfer_functions(name):
     dev = dc.DeviceFns()

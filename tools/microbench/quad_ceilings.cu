@@ -18,8 +18,9 @@ __device__ __forceinline__ void red4(float4* p, float a, float b, float c, float
   asm volatile("red.global.v4.f32.add [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-// MODE 0 gather, 1 red, 2 both
-template <int MODE>
+// MODE 0 gather, 1 red, 2 both; XINNER: 0 = Q[x][y][z] (the two quads of a cell n*n entries apart), 1 = Q[y][z][x] (the
+// two quads of a cell are neighbours), DVR_QUAD_XINNER of diffdvr_b200/csrc/dvr_params.h
+template <int MODE, int XINNER>
 __global__ void __launch_bounds__(128) k(const float4* __restrict__ quad, float4* grad, int n, int iters, float pitch,
                                          int dirsel, float* out) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -32,7 +33,7 @@ __global__ void __launch_bounds__(128) k(const float4* __restrict__ quad, float4
   if (dirsel == 2) { dy = 0.9f; dz = 0.07f; py = 0.3f; pz = ty * pitch; dx = 0.11f; px = tx * pitch + ox; }
   const float sx0 = px, sy0 = py, sz0 = pz;
   float acc = 0.f;
-  const size_t sx = (size_t)n * n;
+  const size_t sxx = (size_t)n * n;
   const float a = 1.0f / 1024.f;
   for (int i = 0; i < iters; ++i) {
     int x0 = int(px), y0 = int(py), z0 = int(pz);
@@ -40,7 +41,8 @@ __global__ void __launch_bounds__(128) k(const float4* __restrict__ quad, float4
       px = sx0 * 0.5f + 0.4f; py = sy0 * 0.5f + 0.4f; pz = sz0 * 0.5f + 0.4f;
       continue;
     }
-    const size_t o = ((size_t)x0 * n + y0) * n + z0;
+    const size_t o = XINNER ? ((size_t)y0 * n + z0) * n + x0 : ((size_t)x0 * n + y0) * n + z0;
+    const size_t sx = XINNER ? 1 : sxx;
     if (MODE == 0 || MODE == 2) {
       const float4 q0 = __ldg(quad + o), q1 = __ldg(quad + o + sx);
       acc += q0.x + q0.y + q0.z + q0.w + q1.x + q1.y + q1.z + q1.w;
@@ -54,17 +56,17 @@ __global__ void __launch_bounds__(128) k(const float4* __restrict__ quad, float4
   if (acc == 12345.678f) out[0] = acc;  // keep the loads alive
 }
 
-template <int MODE>
+template <int MODE, int XINNER>
 double run(const float4* quad, float4* grad, int n, int res, int views, int iters, float pitch, int dir, float* out) {
   dim3 grid(res / 16, res / 8, views);
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0); cudaEventCreate(&e1);
-  k<MODE><<<grid, 128>>>(quad, grad, n, iters, pitch, dir, out);  // warm-up
+  k<MODE, XINNER><<<grid, 128>>>(quad, grad, n, iters, pitch, dir, out);  // warm-up
   cudaDeviceSynchronize();
   float best = 1e30f;
   for (int rep = 0; rep < 3; ++rep) {
     cudaEventRecord(e0);
-    k<MODE><<<grid, 128>>>(quad, grad, n, iters, pitch, dir, out);
+    k<MODE, XINNER><<<grid, 128>>>(quad, grad, n, iters, pitch, dir, out);
     cudaEventRecord(e1);
     cudaEventSynchronize(e1);
     float ms;
@@ -76,9 +78,8 @@ double run(const float4* quad, float4* grad, int n, int res, int views, int iter
   return cells / best * 1e-6;  // Gcells/s
 }
 
-int main() {
-  float* out;
-  cudaMalloc(&out, 4);
+template <int XINNER>
+int measure(float* out) {
   for (int n : {256, 512}) {
     const size_t N = (size_t)n * n * n;
     float4 *quad, *grad;
@@ -92,20 +93,31 @@ int main() {
     const float pitch = 0.6f;  // voxels between neighbouring rays at the volume centre for both C4 and C5
     double g[3], r[3], b[3], hg = 0, hr = 0, hb = 0;
     for (int d = 0; d < 3; ++d) {
-      g[d] = run<0>(quad, grad, n, res, views, iters, pitch, d, out);
-      r[d] = run<1>(quad, grad, n, res, views, iters, pitch, d, out);
-      b[d] = run<2>(quad, grad, n, res, views, iters, pitch, d, out);
+      g[d] = run<0, XINNER>(quad, grad, n, res, views, iters, pitch, d, out);
+      r[d] = run<1, XINNER>(quad, grad, n, res, views, iters, pitch, d, out);
+      b[d] = run<2, XINNER>(quad, grad, n, res, views, iters, pitch, d, out);
       hg += 1.0 / g[d]; hr += 1.0 / r[d]; hb += 1.0 / b[d];
     }
     cudaError_t e = cudaDeviceSynchronize();
-    printf("{\"n\": %d, \"footprint_mib\": %zu, \"rays\": %d, \"pitch_voxels\": %.2f, "
+    printf("{\"layout\": \"%s\", \"n\": %d, \"footprint_mib\": %zu, \"rays\": %d, \"pitch_voxels\": %.2f, "
            "\"gather_gcells_s\": %.2f, \"red_gcells_s\": %.2f, \"gather_red_gcells_s\": %.2f, "
            "\"gather_by_dir_zxy\": [%.2f, %.2f, %.2f], \"red_by_dir_zxy\": [%.2f, %.2f, %.2f], "
            "\"gather_red_by_dir_zxy\": [%.2f, %.2f, %.2f], \"status\": \"%s\"}\n",
-           n, N * 16 >> 20, res * res * views, pitch, 3.0 / hg, 3.0 / hr, 3.0 / hb, g[0], g[1], g[2], r[0], r[1], r[2],
-           b[0], b[1], b[2], cudaGetErrorString(e));
+           XINNER ? "yzx" : "xyz", n, N * 16 >> 20, res * res * views, pitch, 3.0 / hg, 3.0 / hr, 3.0 / hb, g[0], g[1], g[2],
+           r[0], r[1], r[2], b[0], b[1], b[2], cudaGetErrorString(e));
     cudaFree(quad); cudaFree(grad);
     if (e != cudaSuccess) return 1;
   }
   return 0;
+}
+
+// usage: quad_ceilings [xyz | yzx | both]   (default: both layouts, one JSON line per layout and volume size)
+int main(int argc, char** argv) {
+  float* out;
+  cudaMalloc(&out, 4);
+  const char* which = argc > 1 ? argv[1] : "both";
+  int rc = 0;
+  if (which[0] == 'x' || which[0] == 'b') rc |= measure<0>(out);
+  if (which[0] == 'y' || which[0] == 'b') rc |= measure<1>(out);
+  return rc;
 }

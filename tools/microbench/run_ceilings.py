@@ -23,12 +23,14 @@ def clocks():
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default=os.path.join(HERE, "..", "..", "gpurun_out", "MEASURED_GATHER_RED.json"))
+    ap.add_argument("--layout", default="yzx", choices=["xyz", "yzx"],
+                    help="QUAD layout whose ceilings go into by_volume (the other one is kept under other_layout)")
     a = ap.parse_args()
     exe = os.path.join(HERE, "quad_ceilings")
     src = exe + ".cu"
     if not os.path.exists(exe) or os.path.getmtime(exe) < os.path.getmtime(src):
         subprocess.run(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-o", exe, src], check=True)
-    p = subprocess.Popen([exe], stdout=subprocess.PIPE, text=True)
+    p = subprocess.Popen([exe, "both"], stdout=subprocess.PIPE, text=True)
     time.sleep(1.0)
     under_load = clocks()
     out, _ = p.communicate(timeout=600)
@@ -36,7 +38,9 @@ def main():
     res = {"how": "tools/microbench/quad_ceilings.cu: 2 x LDG.128 / 2 x red.v4 per cell on the QUAD layout, 8x4-ray warp "
                   "tiles, one new cell per iteration, best of 3, harmonic mean over three ray directions",
            "when": time.strftime("%Y-%m-%dT%H:%M:%SZ", time.gmtime()), "clocks_under_load": under_load,
-           "by_volume": {str(r["n"]): r for r in rows}}
+           "layout": a.layout,
+           "by_volume": {str(r["n"]): r for r in rows if r.get("layout") == a.layout},
+           "other_layout": {str(r["n"]): r for r in rows if r.get("layout") != a.layout}}
     os.makedirs(os.path.dirname(os.path.abspath(a.out)), exist_ok=True)
     with open(a.out, "w") as f:
         json.dump(res, f, indent=1)
