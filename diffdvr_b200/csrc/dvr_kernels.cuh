@@ -30,10 +30,13 @@ __global__ void __launch_bounds__(kThreads) k_forward(const RayInputs in, const 
   if constexpr (FILTER == kFilterTrilinearQuad && DVR_LOOKAHEAD) {
     // look-ahead loop (Sampler::lookahead): same samples, same arithmetic, the next cell's loads issued one sample early
     [[maybe_unused]] const float sa = smem[0], sc = smem[1];
+    // With predicated loads the look-ahead is unconditional: past the last sample it requests a clamped, valid quad
+    // (Sampler::quad_index) that nobody interpolates, and the loop body has no reconvergence point.
+    constexpr bool ALWAYS = DVR_PRED_LOADS && DVR_BRANCHFREE_CELL && (TF == kTfIdentity || TF == kTfTexture);
     float t = sample_t(ray, 0.f);
-    if (!(t > ray.tmax)) {
+    if (ALWAYS || !(t > ray.tmax)) {
       const f3 p = sample_pos<false>(ray, t);
-      smp.lookahead_f(in, p.x, p.y, p.z);
+      smp.template lookahead_f<ALWAYS>(in, p.x, p.y, p.z);
     }
     for (;;) {
       if (t > ray.tmax) break;
@@ -41,19 +44,19 @@ __global__ void __launch_bounds__(kThreads) k_forward(const RayInputs in, const 
       const float density = smp.interp_f();
       fi += 1.0f;
       t = sample_t(ray, fi);
-      if (!(t > ray.tmax)) {
+      if (ALWAYS || !(t > ray.tmax)) {
         const f3 p = sample_pos<false>(ray, t);
-        smp.lookahead_f(in, p.x, p.y, p.z);
+        smp.template lookahead_f<ALWAYS>(in, p.x, p.y, p.z);
       }
       if constexpr (TF == kTfIdentity) {
         const float dc = fmaxf(0.f, fminf(density, 1.f));
-        const float alpha = blend_alpha<BLEND>(dc * sa, ray.step);
+        const float alpha = blend_alpha<BLEND, ALWAYS>(dc * sa, ray.step);
         const float om = 1.f - acc.w;
         acc.x = fmaf(om * (dc * sc), alpha, acc.x);
         acc.w = fmaf(om, alpha, acc.w);
       } else {
         const f4 cur = tf_eval<TF>(smem, in.R, density);
-        acc = blend_over(acc, cur, blend_alpha<BLEND>(cur.w, ray.step));
+        acc = blend_over(acc, cur, blend_alpha<BLEND, ALWAYS>(cur.w, ray.step));
       }
     }
     if constexpr (TF == kTfIdentity) acc.y = acc.z = acc.x;
