@@ -124,7 +124,11 @@ template <> struct TfChannels<kTfIdentity> { static constexpr int v = 2; };
 template <> struct TfChannels<kTfTexture> { static constexpr int v = 4; };
 template <> struct TfChannels<kTfLinear> { static constexpr int v = 5; };
 
-template <int TF, int TFACC>
+// FACTORED (Texture table, kTfAccSmem, Beer-Lambert on the transmittance; texture_adjoint_factored below): the three
+// colour adjoints of a ray never change along it, so the colour channels of a row's gradient are adjColour.c x (sum of
+// kc w over the samples): the window keeps ONE colour sum and the alpha sum per row (kq[k] = (K, A)) and multiplies by
+// the ray's colour adjoints when a row leaves the window.
+template <int TF, int TFACC, bool FACTORED = false>
 struct TfGrad {
   static constexpr int CH = TfChannels<TF>::v;
   static constexpr int NREG = TFACC == kTfAccReg ? kRegRows * CH : 1;
@@ -137,6 +141,8 @@ struct TfGrad {
   int base;
   int rows;          // R
   float* table;      // kTfAccSmem: this warp's table
+  float2 kq[2];      // FACTORED: (sum kc w, sum adjW w) of the window's two rows
+  float cx, cy, cz;  // FACTORED: the ray's colour adjoints
 
   DVR_DEV void init(float* warpTable, int R) {
 #pragma unroll
@@ -146,9 +152,18 @@ struct TfGrad {
     base = kNoBase;
     rows = R;
     table = warpTable;
+    kq[0] = kq[1] = make_float2(0.f, 0.f);
+    cx = cy = cz = 0.f;
   }
+  DVR_DEV void set_colour_adjoint(float x, float y, float z) { cx = x; cy = y; cz = z; }
   DVR_DEV void flush_rows() {
-    if (base != kNoBase) {
+    if constexpr (FACTORED) {
+      if (base != kNoBase) {
+        flush_one(0);
+        flush_one(1);
+        kq[0] = kq[1] = make_float2(0.f, 0.f);
+      }
+    } else if (base != kNoBase) {
       int r0 = base, r1 = base + 1;
       if constexpr (TF == kTfTexture) {
         r0 = min(max(r0, 0), rows - 1);
@@ -169,10 +184,20 @@ struct TfGrad {
   DVR_DEV void flush_one(int k) {
     int r = base + k;
     if constexpr (TF == kTfTexture) r = min(max(r, 0), rows - 1);
+    if constexpr (FACTORED) {
+      const float2 v = k ? kq[1] : kq[0];
+      if (v.x != 0.f) {
+        atomicAdd(table + r * CH, cx * v.x);
+        atomicAdd(table + r * CH + 1, cy * v.x);
+        atomicAdd(table + r * CH + 2, cz * v.x);
+      }
+      if (v.y != 0.f) atomicAdd(table + r * CH + 3, v.y);
+    } else {
 #pragma unroll
-    for (int c = 0; c < CH; ++c) {
-      const float v = k ? row[1][c] : row[0][c];
-      if (v != 0.f) atomicAdd(table + r * CH + c, v);
+      for (int c = 0; c < CH; ++c) {
+        const float v = k ? row[1][c] : row[0][c];
+        if (v != 0.f) atomicAdd(table + r * CH + c, v);
+      }
     }
   }
   DVR_DEV void add_pair(int key, const float* v, float w) {
@@ -197,6 +222,25 @@ struct TfGrad {
       row[0][c] = fmaf(v[c], w0, row[0][c]);
       row[1][c] = fmaf(v[c], w, row[1][c]);
     }
+  }
+  // FACTORED: the sample lies between rows (key, key + 1) with weights (1 - w, w); kc = the factor of the colour adjoints
+  // in the adjoint of the interpolated colour, adjW = the adjoint of the interpolated absorption
+  DVR_DEV void add_pair_k(int key, float kc, float adjW, float w) {
+    if (key != base) {
+      if (key == base + 1) {
+        flush_one(0);
+        kq[0] = kq[1]; kq[1] = make_float2(0.f, 0.f);
+      } else if (key == base - 1) {
+        flush_one(1);
+        kq[1] = kq[0]; kq[0] = make_float2(0.f, 0.f);
+      } else {
+        flush_rows();
+      }
+      base = key;
+    }
+    const float2 ka = make_float2(kc, adjW);
+    kq[0] = pk_fma(1.f - w, ka, kq[0]);
+    kq[1] = pk_fma(w, ka, kq[1]);
   }
   // contribution v[0..CH) to row r (register accumulators, or straight into the shared table)
   DVR_DEV void add_row(int r, const float* v) {
@@ -414,6 +458,41 @@ DVR_DEV float tf_adjoint(const float* s_tf, int R, float density, const f4& adjC
   }
 }
 
+// Texture TF + Beer-Lambert on the transmittance, evaluation / blend adjoint / TF adjoint of one sample in one piece
+// (DVR_TF_FACTORED). The adjoint never needs the interpolated COLOUR, only S = adjColour . colour, and the colour
+// adjoints are constants of the ray: with q_i = adjColour . row_i (3 FMAs per row), S = q0 + df (q1 - q0), the colour
+// part of d loss / d df is kc (q1 - q0), and the TF gradient of the colour channels is adjColour.c x sum(kc w) (the
+// factored window of TfGrad). 41 FMA-pipe operations per sample instead of 51 (tf_eval_cached + blend_adjoint_T +
+// tf_adjoint); same algebra, sums re-associated.
+#ifndef DVR_TF_FACTORED
+#define DVR_TF_FACTORED 1
+#endif
+template <int TFACC, bool FACTORED>
+DVR_DEV float texture_adjoint_factored(const float* s_tf, int R, float density, float& T, f4& adjAcc, float step,
+                                       TfGrad<kTfTexture, TFACC, FACTORED>& tfg, float& adjStep) {
+  int i0, i1, fl;
+  float df;
+  texture_coords(density, R, i0, i1, df, fl);
+  const f4 v0 = lds4(s_tf + 4 * i0), v1 = lds4(s_tf + 4 * i1);
+  const float q0 = fmaf(adjAcc.z, v0.z, fmaf(adjAcc.y, v0.y, adjAcc.x * v0.x));
+  const float q1 = fmaf(adjAcc.z, v1.z, fmaf(adjAcc.y, v1.y, adjAcc.x * v1.x));
+  const float d3 = q1 - q0;
+  const float S = fmaf(df, d3, q0);
+  const float dvw = v1.w - v0.w;
+  const float curw = fmaf(df, dvw, v0.w);              // the absorption the forward pass blended (tf_eval)
+  const float e = blend_exp(-curw * step);
+  const float alpha = 1.f - e;
+  const float Tin = T * rcp_refined(e);
+  const float kc = alpha * Tin;
+  const float adjAlphaE = (adjAcc.w + S) * T;
+  adjAcc.w = fmaf(-S, alpha, adjAcc.w * e);
+  adjStep = adjAlphaE * curw;
+  const float adjW = adjAlphaE * step;
+  T = Tin;
+  if constexpr (FACTORED) tfg.add_pair_k(fl, kc, adjW, df);
+  return fmaf(kc, d3, adjW * dvw) * float(R);
+}
+
 // Which per-ray gradients the instance carries: none, the stepsize only (one accumulator; C5), or the camera's ray
 // start / direction (+ the stepsize when AdjointArgs::hasStep)
 enum : int { kRayNone = 0, kRayStep = 1, kRayCam = 2 };
@@ -463,7 +542,15 @@ __global__ void __launch_bounds__(kThreads, adjoint_min_ctas<FILTER, TF, HAS_VOL
   int x, y;
   thread_pixel(x, y);
   const bool active = x < in.W && y < in.H;
-  TfGrad<TF, TFACC> tfg;
+  // Beer-Lambert: the loop carries the transmittance in acc.w (blend_adjoint_T). Not in the instances that differentiate
+  // the ray position: their config-size gradients sit within 1e-4 of the fp32 reference build only because the
+  // inversion rounds like the reference's (with T they move to 8e-4 from it -- and from 8.6e-4 to 3.3e-4 from the
+  // reference's fp64 build, profiles/r02_xinner.md; the parity gate is the fp32 build)
+  constexpr bool TMODE = BLEND == kBlendBeer && DVR_BLEND_T && RAY != kRayCam;
+  // Texture tables: the factored sample adjoint (texture_adjoint_factored), with the factored window when the instance
+  // accumulates the TF gradient in shared memory
+  constexpr bool TEXF = TMODE && TF == kTfTexture && TFACC != kTfAccReg && DVR_TF_FACTORED;
+  TfGrad<TF, TFACC, TEXF && TFACC == kTfAccSmem> tfg;
   tfg.init(TFACC == kTfAccSmem ? s_acc + warp * entries : s_acc, in.R);
 
   if (active) {
@@ -487,12 +574,8 @@ __global__ void __launch_bounds__(kThreads, adjoint_min_ctas<FILTER, TF, HAS_VOL
       smp.init(in, b, aa.adjVolume, aa.avB);
     // terminationIndex-1 was the last sample that contributed (renderer_kernels.cuh:374-376)
     float fi = float(n - 1);
-    // Beer-Lambert: the loop carries the transmittance in acc.w (blend_adjoint_T). Not in the instances that differentiate
-    // the ray position: their config-size gradients sit within 1e-4 of the fp32 reference build only because the
-    // inversion rounds like the reference's (with T they move to 8e-4 from it -- and from 8.6e-4 to 3.3e-4 from the
-    // reference's fp64 build, profiles/r02_xinner.md; the parity gate is the fp32 build)
-    constexpr bool TMODE = BLEND == kBlendBeer && DVR_BLEND_T && RAY != kRayCam;
     if constexpr (TMODE) acc.w = 1.f - acc.w;
+    if constexpr (TEXF) tfg.set_colour_adjoint(adjAcc.x, adjAcc.y, adjAcc.z);
     // Identity TF: ray constants of blend_adjoint_grey
     [[maybe_unused]] const float idSa = s_tf[0], idSc = s_tf[1];
     [[maybe_unused]] const float idKS = (adjAcc.x + adjAcc.y + adjAcc.z) * idSc;
@@ -571,6 +654,8 @@ __global__ void __launch_bounds__(kThreads, adjoint_min_ctas<FILTER, TF, HAS_VOL
           tfg.add_row(0, v);
         }
         adjDensity = (density > 0.f && density < 1.f) ? adjDc : 0.f;
+      } else if constexpr (TEXF) {
+        adjDensity = texture_adjoint_factored(s_tf, in.R, density, acc.w, adjAcc, ray.step, tfg, adjStepBlend);
       } else {
         TfCache<TF> tfCache;
         const f4 cur = tf_eval_cached<TF>(s_tf, in.R, density, tfCache);
