@@ -269,6 +269,9 @@ __global__ void __launch_bounds__(kThreads, N <= 6 ? 4 : 3) k_forward_gradients(
 // sample for all seven), colour tangents = dTF/d density x density tangent (rank one), blend tangents written out per
 // input with the shared factors hoisted. ONE marching pass for any D; the slots are assembled at the end (several
 // inputs may share a slot: their tangents add, as unit seeds in the same slot would).
+#ifndef DVR_FWD_RANK1
+#define DVR_FWD_RANK1 1
+#endif
 template <int FILTER, int TF, int BLEND>
 __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const RayInputs in, const ForwardOutputs out,
                                                                           const ForwardGradArgs ga) {
@@ -380,6 +383,32 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
     }
     const float om = 1.f - acc.w;
     const float oav = om * av;
+#if DVR_FWD_RANK1
+    // Every input's colour tangent is (d colour / d density) x (that input's density tangent), so the product rule of
+    // the blend collapses to TWO sample-wide vectors: with E = d alpha / d (w s), B = om E cs.w s and the tangent of
+    // om alpha being -alpha aw_k + B dd_k (+ om E w for the stepsize input, whose s' = 1),
+    //   a.c_k += Q_c dd_k - P_c aw_k,  Q_c = cs.c om alpha + cv.c B,  P_c = cv.c alpha;   aw_k = aw_k (1 - alpha) + B dd_k
+    // -- 16 FMA-pipe operations per input pair instead of 28 (same sums, re-associated).
+    float E;
+    if constexpr (BLEND == kBlendBeer) E = e;
+    else E = active ? 1.f : 0.f;
+    const float omE = om * E;
+    const float Bq = omE * (cs.w * sv), Cw = omE * wv, keep = 1.f - av;
+    const float Qx = fmaf(cv.x, Bq, cs.x * oav), Qy = fmaf(cv.y, Bq, cs.y * oav), Qz = fmaf(cv.z, Bq, cs.z * oav);
+    const float Px = -(cv.x * av), Py = -(cv.y * av), Pz = -(cv.z * av);
+#pragma unroll
+    for (int j = 0; j < NP; ++j) {
+      ax[j] = pk_fma(Px, aw[j], pk_fma(Qx, dd[j], ax[j]));
+      ay[j] = pk_fma(Py, aw[j], pk_fma(Qy, dd[j], ay[j]));
+      az[j] = pk_fma(Pz, aw[j], pk_fma(Qz, dd[j], az[j]));
+      aw[j] = pk_fma(Bq, dd[j], pk_mul(keep, aw[j]));
+    }
+    // the stepsize input (pair 3, first half): alpha depends on it directly as well
+    ax[3].x = fmaf(cv.x, Cw, ax[3].x);
+    ay[3].x = fmaf(cv.y, Cw, ay[3].x);
+    az[3].x = fmaf(cv.z, Cw, az[3].x);
+    aw[3].x += Cw;
+#else
     const float kx = cs.x * oav, ky = cs.y * oav, kz = cs.z * oav, kw = cs.w * sv;
 #pragma unroll
     for (int j = 0; j < NP; ++j) {
@@ -394,6 +423,7 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
       az[j] = pk_add(az[j], pk_fma(kz, dd[j], pk_mul(cv.z, oad)));
       aw[j] = pk_add(aw[j], oad);
     }
+#endif
     acc.x = fmaf(om * cv.x, av, acc.x);
     acc.y = fmaf(om * cv.y, av, acc.y);
     acc.z = fmaf(om * cv.z, av, acc.z);

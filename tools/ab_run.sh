@@ -7,6 +7,6 @@ for v in "$@"; do
   lib=$PWD/diffdvr_b200/libdvr_b200_$v.so
   [ "$v" = default ] && lib=$PWD/diffdvr_b200/libdvr_b200.so
   echo "== $v ($lib)"
-  DVR_LIB_PATH=$lib timeout 300 python tools/bench_configs.py --reps ${REPS:-5} --out gpurun_out/ab_$v.md > gpurun_out/ab_$v.jsonl 2> gpurun_out/ab_$v.err
+  DVR_LIB_PATH=$lib timeout 300 python tools/bench_configs.py --reps ${REPS:-5} --configs ${CONFIGS:-C1,C2,C3,C4,C5} --out gpurun_out/ab_$v.md > gpurun_out/ab_$v.jsonl 2> gpurun_out/ab_$v.err
   echo "rc=$? $(grep -c config gpurun_out/ab_$v.jsonl) configs"
 done
