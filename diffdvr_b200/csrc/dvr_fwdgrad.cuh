@@ -317,8 +317,12 @@ __global__ void __launch_bounds__(kThreads, 4) k_forward_gradients_inputs(const 
     float density;
     [[maybe_unused]] f3 gCell = {0.f, 0.f, 0.f};
     if constexpr (LOOKAHEAD) {
+#if DVR_GRAD_SHARED
+      density = smp.interp_grad(gCell);  // value and cell gradient from one lerp chain, before the look-ahead overwrites either
+#else
       density = smp.interp_f();
       gCell = smp.unit_gradient();   // from the same corner values and fractions, before either is overwritten
+#endif
       tNext = sample_t(ray, fi + 1.0f);
       if (!(tNext > ray.tmax)) {
         const f3 pn = sample_pos<true>(ray, tNext);

@@ -624,8 +624,12 @@ __global__ void __launch_bounds__(kThreads, adjoint_min_ctas<FILTER, TF, HAS_VOL
       if constexpr (LOOKAHEAD) {
         t = tCur;
         p = pCur;
-        density = smp.interp(p.x, p.y, p.z);
-        if constexpr (HAS_RAY) gUnit = smp.unit_gradient();
+        if constexpr (HAS_RAY && DVR_GRAD_SHARED) {
+          density = smp.interp_grad(p.x, p.y, p.z, gUnit);
+        } else {
+          density = smp.interp(p.x, p.y, p.z);
+          if constexpr (HAS_RAY) gUnit = smp.unit_gradient();
+        }
         // the corner registers are dead from here on: the previous sample's cell loads run under this sample's arithmetic
         const float fn = fi - 1.0f;
         if (fn >= 0.f) {
