@@ -41,9 +41,10 @@ struct RayInputs {
   const float* volume;
   long long volB;
   int sx, sy, sz;
-  // QUAD copy (kFilterTrilinearQuad): Q[b][x][y][z] = (v[y][z], v[y][z'], v[y'][z], v[y'][z']) of slice min(x, X-1)
+  // QUAD copy (kFilterTrilinearQuad): quad (x, y, z) = (v[y][z], v[y][z'], v[y'][z], v[y'][z']) of slice min(x, X-1)
   // for x in [0, X] (X + 1 slices: the far-face clamp of x is a duplicated last slice), y' = min(y+1, Y-1),
-  // z' = min(z+1, Z-1): one cell = 2 aligned 16-byte loads at quad offsets q and q + Y*Z, no clamp in the kernel
+  // z' = min(z+1, Z-1), stored as Q[b][y][z][x] (DVR_QUAD_XINNER, the default: one cell = 2 aligned 16-byte loads at
+  // quad offsets q and q + 1) or Q[b][x][y][z] (DVR_QUAD_XINNER = 0: q and q + Y*Z); no clamp in the kernel
   const float4* quads;
   long long quadB;                   // float4 elements per batch entry, (X+1)*Y*Z (0: one volume for all views)
   // hoisted index arithmetic of the QUAD cell load: q = ux*quadYZ + uy*Z + uz - quadBias on the biased-float bit
